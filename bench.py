@@ -1,0 +1,307 @@
+#!/usr/bin/env python
+"""bench.py -- Gray-Scott timesteps/s on a synthetic icosphere (BASELINE.json metric) + the HBM roofline of the
+dominant PCG kernel, next to the reference's Eigen CPU path.
+
+    python bench.py --gpus 1 --steps K --warmup W            our arm (libfeab.so through the C ABI)
+    python bench.py --impl reference --steps K --warmup W    the reference's CPU implementation (oracle/_ref)
+    torchrun ... bench.py --gpus N ...                       N ranks, one mesh partition... see DESIGN.md (e)
+
+A "step" is one Gray-Scott time step (two Jacobi-PCG solves run to Eigen's stopping rule) of the whole mesh.
+`value` keeps the field device-resident (feab_step(NULL, K, 0)); `e2e` drives the same K steps through the
+reference-facing call with a pinned HOST values buffer, one host->device and one device->host copy per step.
+Prints ONE JSON line on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+GS = dict(dt=0.001, Du=0.08, Dv=0.04, f=0.035, k=0.06)   # include/FEM/EquationParameters.hpp:43-49
+EQ_GS = 3
+
+
+def env_int(name, default):
+    try:
+        return int(os.environ.get(name, default))
+    except ValueError:
+        return default
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    def __init__(self, index=0):
+        self.rows = []
+        self.proc = None
+        self.index = index
+
+    def start(self):
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx.append(float(r[1]))
+                for nm, val in zip(names, r[3:7]):
+                    if val.lower().startswith("active"):
+                        reasons.add(nm)
+            except Exception:
+                continue
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def build_mesh(nu):
+    from fea_visualizer_b200 import meshes
+    xyz, tri = meshes.icosphere(nu)
+    ob = np.zeros(len(xyz), dtype=np.uint8)   # closed surface: no boundary nodes (checked by tests/test_meshes.py)
+    return xyz, tri, ob
+
+
+def seed_protocol(F, V, nsteps):
+    """50 seed nodes = 1.0 before step 0, re-applied before each of the first 5 steps."""
+    from fea_visualizer_b200 import meshes
+    seeds = meshes.seed_nodes(V)
+    for s in range(nsteps):
+        if s < 5:
+            F.brush(seeds, 1.0)
+        F.step(1)
+
+
+# ------------------------------------------------------------------------------------------------ CPU reference
+def cpu_reference(sample_nu, steps, warmup, threads, target_rows=None):
+    """Times the UNMODIFIED reference (Eigen fp32 Jacobi-PCG, oracle/_ref/libfea_ref_fast.so) on a bounded sample of
+    the workload: the same Gray-Scott protocol on a smaller icosphere from the same generator.  Returns steps/s of the
+    sample and the figure converted to the target mesh by rows x iterations (iterations ~ sqrt(rows), measured
+    scaling recorded in BASELINE.md)."""
+    from fea_visualizer_b200 import meshes
+    from oracle import oracle as O
+    fast = O.reference_available(fast=True)
+    if not (fast or O.reference_available()):
+        return None
+    xyz, tri, ob = build_mesh(sample_nu)
+    V = len(xyz)
+    t0 = time.perf_counter()
+    R = O.Reference(xyz, tri, ob, 0, fast=fast)
+    t_asm = time.perf_counter() - t0
+    used = R.set_threads(threads) if fast else 1
+    R.set_equation(EQ_GS)
+    seeds = meshes.seed_nodes(V)
+    vals = np.zeros(V, np.float32)
+    done = 0
+    times = []
+    for s in range(warmup + steps):
+        if s < 5:
+            vals = R.get_values()
+            vals[seeds] = 1.0
+            R.set_values(vals)
+        t0 = time.perf_counter()
+        R.step(1)
+        dt = time.perf_counter() - t0
+        if s >= warmup:
+            times.append(dt)
+        done += 1
+    sps = len(times) / sum(times)
+    out = {"sample_steps_per_s": sps, "sample_rows": V, "assembly_s": t_asm, "cores": used, "kind": "reference",
+           "build": "fast(-O3 -march=x86-64-v3 -fopenmp)" if fast else "pin(-O2)"}
+    if target_rows:
+        ratio = (target_rows / V) ** 1.5     # rows x iterations, iterations ~ sqrt(rows) at fixed dt
+        out["converted_steps_per_s"] = sps / ratio
+        out["conversion"] = f"(rows_target/rows_sample)^1.5 = {ratio:.2f}"
+    return out
+
+
+# ------------------------------------------------------------------------------------------------ main
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--nu", type=int, default=env_int("FEAB_BENCH_NU", 1265), help="icosphere frequency; 1265 = 16 002 252 vertices")
+    ap.add_argument("--real", type=int, default=64, choices=[32, 64])
+    ap.add_argument("--cpu-nu", type=int, default=env_int("FEAB_BENCH_CPU_NU", 316))
+    ap.add_argument("--cpu-steps", type=int, default=3)
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--tol", type=float, default=-1.0, help="<0: epsilon of the arithmetic type (Eigen default)")
+    args = ap.parse_args()
+
+    rank = env_int("RANK", 0)
+    world = env_int("WORLD_SIZE", 1)
+    local_rank = env_int("LOCAL_RANK", 0)
+    V_target = 10 * args.nu * args.nu + 2
+    workload = f"gray-scott icosphere nu={args.nu} ({V_target} vertices, {20 * args.nu * args.nu} triangles), reference default parameters"
+    ncores = os.cpu_count() or 1
+
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        warm = max(1, min(args.warmup, 2))
+        res = cpu_reference(args.cpu_nu, max(1, min(args.steps, 5)), warm, ncores, target_rows=V_target)
+        if res is None:
+            print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref not built"}))
+            return 0
+        val = res["converted_steps_per_s"]
+        line = {"metric": "gray_scott_timesteps_per_s", "value": val, "unit": "steps/s", "n_gpus": args.gpus, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": 1e3 / val, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f32", "data": "synthetic", "impl": "reference",
+                "config": {"workload": workload, "timed_on": f"icosphere nu={args.cpu_nu} ({res['sample_rows']} vertices)",
+                           "conversion": res["conversion"]},
+                "cpu_baseline": {"value": val, "unit": "steps/s", "cores": res["cores"], "kind": res["kind"],
+                                 "sample": f"{res['sample_steps_per_s']:.4f} steps/s measured on icosphere nu={args.cpu_nu} "
+                                           f"({res['sample_rows']} rows), converted by {res['conversion']}; {res['build']}"},
+                "e2e": {"value": val, "unit": "steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                "gpu_launches": 0}
+        print(json.dumps(line))
+        return 0
+
+    import torch
+    import torch.distributed as dist
+    from fea_visualizer_b200 import feab
+
+    if not torch.cuda.is_available():
+        print(json.dumps({"error": "no CUDA device: libfeab has no CPU fallback"}))
+        return 1
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    torch.cuda.set_device(local_rank)
+
+    # weak scaling over independent replicas of the mesh until the partitioned solver lands (DESIGN.md section e)
+    xyz, tri, ob = build_mesh(args.nu)
+    V = len(xyz)
+    F = feab.Feab(real=args.real, device=local_rank)
+    if args.tol >= 0:
+        F.set_solver(tolerance=args.tol)
+    t0 = time.perf_counter()
+    F.set_mesh(xyz, tri, ob)
+    setup_s = time.perf_counter() - t0
+    _, n, nnz, max_row = F.counts()
+    F.set_equation(EQ_GS)
+    F.set_params(EQ_GS, GS["dt"], GS["Du"], GS["Dv"], GS["f"], GS["k"])
+    F.clear()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # warm-up (includes the seed protocol of the first 5 steps)
+    seed_protocol(F, V, max(args.warmup, 3))
+    launches0 = F.stats()["kernel_launches"]
+
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    # --- device-resident timed region ---
+    barrier()
+    F.step(args.steps)                       # K steps in one call; CUDA events on the solver stream bracket it inside
+    barrier()
+    st = F.stats()
+    ms = st["last_call_ms"]
+    its = st["iterations"]
+    launches = st["kernel_launches"] - launches0
+    # --- end-to-end through the reference-facing call with HOST buffers ---
+    host = torch.empty(V, dtype=torch.float32).pin_memory()
+    host.copy_(torch.from_numpy(F.get_values()))
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        F.step_ptr(host.data_ptr(), 1, True)  # H2D of values, one step, D2H of values, synchronised
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+
+    t = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_max, e2e_ms_max = t.tolist()
+
+    # --- roofline of the dominant kernel (SpMV + dot), measured live with CUDA events on the solver stream ---
+    roof = None
+    kernels = {}
+    if rank == 0:
+        peak, peak_src = measured_peak()
+        for kid, name in ((0, "spmv_dot"), (1, "cg_update"), (2, "cg_direction"), (3, "rhs_init")):
+            kms, kbytes = F.time_kernel(kid, 20)
+            kernels[name] = {"ms": kms, "algorithmic_bytes": kbytes, "GBps": kbytes / kms / 1e6}
+        k0 = kernels["spmv_dot"]
+        it_ms = kernels["spmv_dot"]["ms"] + kernels["cg_update"]["ms"] + kernels["cg_direction"]["ms"]
+        it_bytes = sum(kernels[k]["algorithmic_bytes"] for k in ("spmv_dot", "cg_update", "cg_direction"))
+        roof = {"bound": "hbm", "kernel": "spmv_dot", "achieved": k0["GBps"], "peak": peak, "unit": "GB/s", "frac": k0["GBps"] / peak,
+                "traffic": None, "peak_source": peak_src, "frac_of_nominal_8TBps": k0["GBps"] / 8000.0,
+                "pcg_iteration": {"ms": it_ms, "algorithmic_bytes": it_bytes, "GBps": it_bytes / it_ms / 1e6,
+                                  "frac": it_bytes / it_ms / 1e6 / peak},
+                "kernels": kernels}
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        res = cpu_reference(args.cpu_nu, args.cpu_steps, 1, ncores, target_rows=V)
+        if res is not None:
+            cpu = {"value": res["converted_steps_per_s"], "unit": "steps/s", "cores": res["cores"], "kind": res["kind"],
+                   "sample": f"{res['sample_steps_per_s']:.4f} steps/s measured on icosphere nu={args.cpu_nu} ({res['sample_rows']} rows, "
+                             f"{args.cpu_steps} steps, fp32 Eigen PCG tol 1.19e-7), converted by {res['conversion']}; {res['build']}"}
+
+    if rank == 0:
+        total_steps = args.steps * world      # replicas: every rank advances its own mesh
+        value = total_steps / (ms_max / 1e3)
+        line = {"metric": "gray_scott_timesteps_per_s", "value": value, "unit": "steps/s", "n_gpus": world, "steps": args.steps,
+                "warmup": max(args.warmup, 3), "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f64" if args.real == 64 else "f32", "data": "synthetic",
+                "config": {"workload": workload, "rows": n, "nnz": nnz, "max_row": max_row, "parallelism": f"replicas x{world}",
+                           "tolerance": "eps of dtype (Eigen default)" if args.tol < 0 else args.tol,
+                           "pcg_iterations_last_step": its, "l2_policy": "inputs larger than L2 (matrix + vectors >> 126 MB)",
+                           "setup_s": setup_s},
+                "e2e": {"value": total_steps / (e2e_ms_max / 1e3), "unit": "steps/s", "h2d_bytes_per_step": 4 * V, "d2h_bytes_per_step": 4 * V},
+                "gpu_launches": int(launches + st["kernel_launches"] * 0), "roofline": roof, "cpu_baseline": cpu, "clocks": clocks}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

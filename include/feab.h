@@ -1,0 +1,150 @@
+/* feab.h -- C ABI of libfeab.so, the B200-native (sm_100a) implementation of fea-visualizer's
+ * time-stepping hot path: P1 triangle mass / stiffness / advection assembly into a CSR system and the
+ * per-timestep Jacobi-PCG (or BiCGSTAB) solve of (M/dt + c K [- Adv]) x = b for the heat, wave,
+ * advection-diffusion and Gray-Scott solvers.
+ *
+ * Plain pointers and sizes only; every pointer argument is a HOST pointer unless it says "device".
+ * Every entry point returns 0 on success, a negative FEAB_E* code or a positive cudaError_t otherwise;
+ * feab_last_error() gives the text.  No exceptions cross this boundary.  A handle is not thread-safe
+ * (the reference's solvers are single-threaded and non-reentrant, src/Application.cpp:506-565).
+ *
+ * Each entry point cites the reference interface it replaces (paths relative to the reference root).
+ * The host-side C++ mirror of the reference classes that calls this ABI is include/FEM/CUDASolver.hpp;
+ * INTEGRATION.md shows the binding a maintainer of the reference would add.
+ */
+#ifndef FEAB_H
+#define FEAB_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct FeabHandle FeabHandle;
+
+/* include/FEM/FEMContext.hpp:9-14 (enum class Equation) */
+enum { FEAB_EQ_HEAT = 0, FEAB_EQ_WAVE = 1, FEAB_EQ_ADVECTION_DIFFUSION = 2, FEAB_EQ_REACTION_DIFFUSION = 3 };
+/* include/FEM/FEMContext.hpp:16-19 (enum class BoundaryCondition) */
+enum { FEAB_BC_DIRICHLET = 0, FEAB_BC_NEUMANN = 1 };
+/* FEMContext's three private matrices, include/FEM/FEMContext.hpp:47-49 */
+enum { FEAB_MAT_MASS = 0, FEAB_MAT_STIFFNESS = 1, FEAB_MAT_ADVECTION = 2 };
+/* Linear solver for the (non-symmetric) advection-diffusion operator.
+ * PARITY_CG reproduces the reference: Eigen::ConjugateGradient<.., Lower|Upper> multiplies by A^T
+ * (lib/eigen/Eigen/src/IterativeLinearSolvers/ConjugateGradient.h:192-208, src/FEM/CPUSolver.cpp:65,98-99).
+ * BICGSTAB solves the same system correctly (Jacobi right-preconditioned, after BiCGSTAB.h:31-119).
+ * The three symmetric equations always use the Jacobi-PCG. */
+enum { FEAB_SOLVER_PARITY_CG = 0, FEAB_SOLVER_BICGSTAB = 1 };
+/* Assembly algorithm.  SCATTER: one thread per triangle, local 3x3 matrices, precomputed CSR scatter map,
+ * atomic adds (diagonal sums are order-dependent in the last bit).  ORDERED: one thread per row summing its
+ * incident triangles in ascending element order -- Eigen's setFromTriplets order
+ * (lib/eigen/Eigen/src/SparseCore/SparseMatrix.h:1475-1511), deterministic. */
+enum { FEAB_ASSEMBLY_SCATTER = 0, FEAB_ASSEMBLY_ORDERED = 1 };
+/* Solve-loop driver: one CUDA graph per step with a device-side WHILE node (no host round trips), or
+ * host-batched iterations with a flag poll per batch. */
+enum { FEAB_LOOP_GRAPH_WHILE = 0, FEAB_LOOP_HOST_BATCHED = 1 };
+
+enum {
+    FEAB_OK = 0,
+    FEAB_EINVAL = -1,   /* bad argument / call order */
+    FEAB_ENOMESH = -2,  /* no mesh set */
+    FEAB_ENOGPU = -3,   /* no CUDA device: there is no CPU fallback */
+    FEAB_ENOMEM = -4
+};
+
+/* include/FEM/EquationParameters.hpp:4-49.  Scalars keep the reference's float type; they are promoted to
+ * the handle's arithmetic type exactly like the reference's values would be.
+ *   Heat:   c[0] = conductivity              Wave: c[0] = c
+ *   AdvDiff: c[0] = c                        ReactionDiffusion: c[0..3] = Du, Dv, feed_rate, kill_rate */
+typedef struct {
+    float time_step;
+    float c[4];
+} FeabParams;
+
+/* Solver controls; the defaults are Eigen's (IterativeSolverBase.h:251, :368). */
+typedef struct {
+    int solver;        /* FEAB_SOLVER_*; default PARITY_CG */
+    double tolerance;  /* on |r|/|b|; < 0 = epsilon of the arithmetic type (Eigen default) */
+    int64_t max_iter;  /* < 0 = 2 n (Eigen default) */
+    int loop_mode;     /* FEAB_LOOP_* */
+    int assembly;      /* FEAB_ASSEMBLY_* */
+} FeabSolverOptions;
+
+typedef struct {
+    int64_t iterations[2];     /* per solve of the last step (Gray-Scott has two) */
+    double rel_residual[2];    /* sqrt(|r|^2/|b|^2) as Eigen reports it (ConjugateGradient.h:83) */
+    double last_call_ms;       /* device time of the last feab_step call (CUDA events on the solver stream) */
+    int64_t last_call_steps;
+    int64_t kernel_launches;   /* kernels launched by this handle since creation (graph nodes counted per execution) */
+    double solve_ms;           /* device time inside the PCG loops of the last call when timing detail is on, else 0 */
+} FeabStats;
+
+/* -- lifetime ------------------------------------------------------------------------------- */
+/* real_bytes: 4 = fp32 (the reference's arithmetic), 8 = fp64.  device: CUDA ordinal.
+ * Replaces the constructors CPUSolver::CPUSolver / FEMContext::FEMContext (src/FEM/CPUSolver.cpp:6-8,
+ * src/FEM/FEMContext.cpp:10-15). */
+int feab_create(int device, int real_bytes, FeabHandle** out);
+int feab_destroy(FeabHandle* h);
+const char* feab_last_error(const FeabHandle* h);
+
+/* -- FEMContext ----------------------------------------------------------------------------- */
+/* FEMContext::init_from_surface (src/FEM/FEMContext.cpp:21-27): takes the Surface data members the
+ * path reads (include/Utils/Surface.hpp:36-40): vertices V x 3 float, triangles T x 3 uint32,
+ * on_boundary V bytes.  Builds idx_map, the CSR pattern, the scatter map, and assembles M, K, Adv. */
+int feab_set_mesh(FeabHandle* h, int64_t num_vertices, const float* xyz, int64_t num_triangles, const uint32_t* tri,
+                  const uint8_t* on_boundary);
+/* fem_ctx->boundary_condition = bc; update_boundary_conditions() (src/FEM/FEMContext.cpp:224-240).
+ * Does NOT touch solver state; callers follow with feab_clear like Application does (src/Application.cpp:313-316). */
+int feab_set_boundary_condition(FeabHandle* h, int bc);
+/* parameters[Advection_Diffusion]->velocity = v; assemble_matrices() (src/FEM/FEMContext.cpp:57-64,
+ * called from src/Application.cpp:393-394).  velocity == NULL keeps the current one (default (1,0,0)). */
+int feab_assemble(FeabHandle* h, const float* velocity3);
+/* num_nodes / num_unknowns / num_max_nonzeros_per_row (src/FEM/FEMContext.cpp:33-52) and nnz of the shared pattern */
+int feab_get_counts(const FeabHandle* h, int64_t* num_nodes, int64_t* num_unknowns, int64_t* nnz, int* max_row_nonzeros);
+/* FEMContext::idx_map (include/FEM/FEMContext.hpp:29) */
+int feab_get_idx_map(FeabHandle* h, int32_t* out_num_nodes);
+/* The assembled matrices, for parity tests: the reference keeps them private (FEMContext.hpp:47-49).
+ * CSR with ascending columns; for the symmetric patterns this equals Eigen's CSC arrays index for index.
+ * Call with all-NULL outputs to get only *nnz.  val has the handle's real type. */
+int feab_get_csr(FeabHandle* h, int which, int64_t* nnz, int32_t* rowptr, int32_t* col, void* val);
+
+/* -- Solver --------------------------------------------------------------------------------- */
+/* fem_ctx->equation = eq (src/Application.cpp:639-641) */
+int feab_set_equation(FeabHandle* h, int equation);
+/* fem_ctx->parameters[eq] fields (edited live by the GUI, src/Application.cpp:373-423); read at every step */
+int feab_set_params(FeabHandle* h, int equation, const FeabParams* params);
+int feab_get_params(const FeabHandle* h, int equation, FeabParams* params);
+int feab_set_solver_options(FeabHandle* h, const FeabSolverOptions* opt);
+int feab_get_solver_options(const FeabHandle* h, FeabSolverOptions* opt);
+/* Solver::clear_values (src/FEM/CPUSolver.cpp:54-59) plus Surface::clear_values as Application::clear_solver
+ * does (src/Application.cpp:579-583): u, v <- 0 (resized to num_unknowns), values <- 0 */
+int feab_clear(FeabHandle* h);
+/* surface->values (include/Utils/Surface.hpp:38), device-resident here */
+int feab_set_values(FeabHandle* h, const float* values_num_nodes);
+int feab_get_values(FeabHandle* h, float* values_num_nodes);
+/* GPUSolver::brush(idx, strength) (include/FEM/GPUSolver.hpp:41, src/FEM/GPUSolver.cpp:44-51) /
+ * Application::brush's write surface->values[node] = strength (src/Application.cpp:722) for many nodes */
+int feab_brush(FeabHandle* h, const int64_t* nodes, int64_t count, float strength);
+/* Solver::advance_time (src/FEM/CPUSolver.cpp:64-147), nsteps times.
+ * values_inout != NULL: copied host->device before the first step (the brush may have written it) and, when
+ * sync_values != 0, device->host after the last one -- the reference's data contract through surface->values.
+ * values_inout == NULL keeps everything device-resident (benchmark mode). */
+int feab_step(FeabHandle* h, float* values_inout, int nsteps, int sync_values);
+/* Solver::has_numerical_instability (src/FEM/CPUSolver.cpp:41-48): any u_i > 1e4 or v_i > 1e4 */
+int feab_unstable(FeabHandle* h, int* out);
+int feab_last_stats(FeabHandle* h, FeabStats* out);
+/* CPUSolver's private u (which = 0) / v (which = 1), length num_unknowns, handle's real type */
+int feab_get_state(FeabHandle* h, int which, void* out);
+int feab_set_state(FeabHandle* h, int which, const void* in);
+
+/* -- measurement hooks (used by bench.py; not part of the reference interface) ---------------- */
+/* Runs `reps` launches of one hot kernel on the current operator and returns the mean device time per
+ * launch (CUDA events on the solver stream) and the algorithmic bytes one launch moves.
+ * kernel: 0 = SpMV+dot, 1 = PCG vector update, 2 = PCG direction update, 3 = RHS build for the current equation */
+int feab_time_kernel(FeabHandle* h, int kernel, int reps, double* ms_per_launch, double* algorithmic_bytes);
+int feab_device_info(const FeabHandle* h, int* sm_count, int64_t* total_mem_bytes, char* name64);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FEAB_H */

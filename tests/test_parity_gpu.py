@@ -1,0 +1,356 @@
+"""GPU parity tests (run on the B200 box with -m gpu): the CUDA path, called through the C ABI, against the CPU
+oracle on the same seeded inputs and against the golden vectors produced by the unmodified reference.
+
+Bars: sparsity pattern and index work bit-exact; fp64 assembled values exactly equal to the fp64 oracle in
+ORDERED mode and within 1e-12 * max|row| in SCATTER mode (atomic order on the diagonal); fields within
+1e-8 relative L2 per step in fp64 (north star); the fp32 build within 5e-6 of the fp32 Eigen reference
+(its own solve tolerance is 1.19e-7 per step).
+"""
+import numpy as np
+import pytest
+
+from fea_visualizer_b200 import feab, meshes
+from oracle import oracle as O
+from tests.util import load_golden, rel_l2, run_steps, small_meshes
+
+pytestmark = pytest.mark.gpu
+
+FP64_STEP_TOL = 1e-8     # BASELINE.json north_star: <= 1e-8 relative L2 per step in fp64
+FP32_REF_TOL = 5e-6      # fp32 build vs the fp32 Eigen reference
+MATS = "MKA"
+
+
+def make(real, xyz, tri, ob, bc, **solver):
+    F = feab.Feab(real=real)
+    F.set_boundary_condition(bc)
+    if solver:
+        F.set_solver(**solver)
+    F.set_mesh(xyz, tri, ob)
+    return F
+
+
+def cases():
+    out = dict(small_meshes())
+    out["ico8d"] = meshes.icosphere(8, displace=True)
+    out["disk14"] = meshes.disk(14)
+    return out
+
+
+# ---------------------------------------------------------------------------------------------- assembly
+@pytest.mark.parametrize("name", ["ico4", "grid", "disk", "ico8d", "disk14"])
+@pytest.mark.parametrize("bc", [0, 1])
+@pytest.mark.parametrize("assembly", [feab.ASSEMBLY_SCATTER, feab.ASSEMBLY_ORDERED])
+def test_assembly_fp64_vs_oracle(name, bc, assembly):
+    xyz, tri = cases()[name]
+    ob = meshes.boundary_flags(len(xyz), tri)
+    D = O.Oracle(xyz, tri, ob, bc, real=64)
+    F = make(64, xyz, tri, ob, bc, assembly=assembly)
+    V, n, nnz, max_row = F.counts()
+    assert (F.idx_map() == D.idx_map()).all()
+    assert n == D.num_unknowns() and max_row == D.max_row_nonzeros()
+    for w, mn in enumerate(MATS):
+        outer, inner, val = D.csc(w)
+        rowptr, col, gval = F.csr(w)
+        # bit-exact pattern: the pattern is structurally symmetric, so CSR arrays == Eigen's CSC arrays
+        assert (rowptr == outer).all() and (col == inner).all(), mn
+        # CSR value at (i, j) is the CSC value at (j, i): transpose the oracle's values through a dense map
+        ref = csc_values_in_csr_order(n, outer, inner, val)
+        if assembly == feab.ASSEMBLY_ORDERED:
+            assert (gval == ref).all(), mn                       # same summation order as Eigen: identical bits
+        else:
+            row_id = np.repeat(np.arange(n), np.diff(rowptr))
+            rowmax = np.zeros(n)
+            np.maximum.at(rowmax, row_id, np.abs(ref))
+            tol = 1e-12 * rowmax[row_id]
+            assert (np.abs(gval - ref) <= tol).all(), mn
+
+
+def csc_values_in_csr_order(n, outer, inner, val):
+    """values of the column-major matrix re-read row by row (row i ascending columns)"""
+    nnz = len(inner)
+    cols = np.repeat(np.arange(n), np.diff(outer))
+    order = np.lexsort((cols, inner))       # sort by row (inner), then column
+    return val[order]
+
+
+@pytest.mark.parametrize("name", ["ico4", "grid", "disk"])
+@pytest.mark.parametrize("bc", [0, 1])
+def test_assembly_fp32_ordered_is_bit_identical_to_eigen(name, bc):
+    """fp32 build, ORDERED assembly: every value of M, K, Adv has exactly the bits Eigen's setFromTriplets produced."""
+    g = load_golden("ref_small.npz")
+    xyz, tri, ob = g[f"{name}/xyz"], g[f"{name}/tri"], g[f"{name}/onb"]
+    F = make(32, xyz, tri, ob, bc, assembly=feab.ASSEMBLY_ORDERED)
+    n = F.num_unknowns()
+    assert (F.idx_map() == g[f"{name}/bc{bc}/idx_map"]).all()
+    for w, mn in enumerate(MATS):
+        outer, inner, val = g[f"{name}/bc{bc}/{mn}/outer"], g[f"{name}/bc{bc}/{mn}/inner"], g[f"{name}/bc{bc}/{mn}/val"]
+        rowptr, col, gval = F.csr(w)
+        assert (rowptr == outer).all() and (col == inner).all()
+        assert (gval == csc_values_in_csr_order(n, outer, inner, val)).all(), mn
+
+
+def test_bundled_meshes_sizes():
+    g = load_golden("ref_assets.npz")
+    for name, bc in (("icosphere", 0), ("tube", 0), ("tube", 1)):
+        xyz, tri, ob = g[f"{name}/xyz"], g[f"{name}/tri"].astype(np.uint32), g[f"{name}/onb"]
+        F = make(64, xyz, tri, ob, bc)
+        V, n, nnz, max_row = F.counts()
+        sizes = g[f"{name}/bc{bc}/sizes"]
+        assert (n, max_row, nnz) == (sizes[0], sizes[1], sizes[2])
+        assert len(F.csr(2)[1]) == sizes[4]
+        for w in range(3):
+            assert abs(F.csr(w)[2].sum() - g[f"{name}/bc{bc}/sums"][w]) <= 2e-5 * max(1.0, abs(g[f"{name}/bc{bc}/sums"][w]))
+
+
+def test_velocity_change_reassembles_and_bc_switch():
+    xyz, tri = meshes.disk(8)
+    ob = meshes.boundary_flags(len(xyz), tri)
+    D = O.Oracle(xyz, tri, ob, 0, real=64)
+    F = make(64, xyz, tri, ob, 0, assembly=feab.ASSEMBLY_ORDERED)
+    vel = [0.3, 0.0, -2.0]
+    D.set_velocity(vel)
+    F.assemble(vel)
+    outer, inner, val = D.csc(2)
+    assert (F.csr(2)[2] == csc_values_in_csr_order(D.num_unknowns(), outer, inner, val)).all()
+    D.set_boundary_condition(1)
+    F.set_boundary_condition(1)
+    assert F.num_unknowns() == len(xyz) == D.num_unknowns()
+    for w in range(3):
+        outer, inner, val = D.csc(w)
+        rowptr, col, gval = F.csr(w)
+        assert (rowptr == outer).all() and (col == inner).all()
+        assert (gval == csc_values_in_csr_order(D.num_unknowns(), outer, inner, val)).all()
+
+
+# ---------------------------------------------------------------------------------------------- time stepping
+@pytest.mark.parametrize("name", ["ico4", "grid", "disk", "ico8d"])
+@pytest.mark.parametrize("bc", [0, 1])
+@pytest.mark.parametrize("eq", [0, 1, 2, 3])
+def test_step_parity_fp64(name, bc, eq):
+    """Per-step relative L2 vs the fp64 oracle <= 1e-8 for every equation (adv-diff in reference-parity mode)."""
+    xyz, tri = cases()[name]
+    ob = meshes.boundary_flags(len(xyz), tri)
+    D = O.Oracle(xyz, tri, ob, bc, real=64)
+    F = make(64, xyz, tri, ob, bc, assembly=feab.ASSEMBLY_ORDERED)
+    worst = [0.0]
+    ref_vals = []
+    run_steps(D, len(xyz), eq, 6, per_step=lambda s, X: ref_vals.append((X.get_values(), X.get_state(0), X.get_state(1), X.last_stats()[0].copy())))
+
+    def check(s, X):
+        v, u, vv, it = ref_vals[s]
+        worst[0] = max(worst[0], rel_l2(X.get_state(0), u), rel_l2(X.get_state(1), vv), rel_l2(X.get_values(), v))
+        git = X.stats()["iterations"]
+        assert abs(git[0] - it[0]) <= 3 and abs(git[1] - it[1]) <= 3, (git, it)
+
+    run_steps(F, len(xyz), eq, 6, per_step=check)
+    assert worst[0] <= FP64_STEP_TOL, worst[0]
+    assert F.unstable() == D.unstable()
+
+
+@pytest.mark.parametrize("name", ["ico4", "grid", "disk"])
+@pytest.mark.parametrize("bc", [0, 1])
+def test_step_fp32_vs_reference_golden(name, bc):
+    """fp32 build vs the fields the unmodified Eigen reference produced (5 steps, all four equations)."""
+    g = load_golden("ref_small.npz")
+    xyz, tri, ob = g[f"{name}/xyz"], g[f"{name}/tri"], g[f"{name}/onb"]
+    F = make(32, xyz, tri, ob, bc)
+    for eq in range(4):
+        got = run_steps(F, len(xyz), eq, 5)
+        assert rel_l2(got, g[f"{name}/bc{bc}/eq{eq}/values5"]) <= FP32_REF_TOL, eq
+
+
+def test_c1_heat_100_steps_on_bundled_icosphere():
+    """BASELINE.json configs[0]: heat on the bundled icosphere.obj, 100 steps."""
+    g = load_golden("ref_assets.npz")
+    xyz, tri, ob = g["icosphere/xyz"], g["icosphere/tri"].astype(np.uint32), g["icosphere/onb"]
+    ref32 = g["icosphere/bc0/eq0/values100"]
+    F32 = make(32, xyz, tri, ob, 0)
+    assert rel_l2(run_steps(F32, len(xyz), 0, 100), ref32) <= 2e-5
+    D = O.Oracle(xyz, tri, ob, 0, real=64)
+    F64 = make(64, xyz, tri, ob, 0)
+    want = run_steps(D, len(xyz), 0, 100)
+    got = run_steps(F64, len(xyz), 0, 100)
+    assert rel_l2(got, want) <= 1e-7          # 100-step drift (values pass through float every step)
+    assert rel_l2(got, ref32) <= 2e-5
+
+
+def test_tube_all_equations_vs_reference_golden():
+    g = load_golden("ref_assets.npz")
+    xyz, tri, ob = g["tube/xyz"], g["tube/tri"].astype(np.uint32), g["tube/onb"]
+    for bc in (0, 1):
+        F = make(32, xyz, tri, ob, bc)
+        for eq in range(4):
+            got = run_steps(F, len(xyz), eq, 20)
+            assert rel_l2(got, g[f"tube/bc{bc}/eq{eq}/values20"]) <= 2e-5, (bc, eq)
+
+
+def test_bicgstab_mode_vs_oracle_and_true_residual():
+    xyz, tri = meshes.icosphere(8)
+    ob = meshes.boundary_flags(len(xyz), tri)
+    n = len(xyz)
+    D = O.Oracle(xyz, tri, ob, 0, real=64)
+    D.set_solver(mode=1)
+    F = make(64, xyz, tri, ob, 0, solver=feab.SOLVER_BICGSTAB, assembly=feab.ASSEMBLY_ORDERED)
+    want = run_steps(D, n, 2, 4)
+    got = run_steps(F, n, 2, 4)
+    assert rel_l2(F.get_state(0), D.get_state(0)) <= FP64_STEP_TOL
+    assert rel_l2(got, want) <= 1e-7
+    assert abs(F.stats()["iterations"][0] - D.last_stats()[0][0]) <= 3
+    # true residual of the last solve: rebuild A and b densely from the exported CSR matrices
+    P = make(64, xyz, tri, ob, 0, solver=feab.SOLVER_PARITY_CG, assembly=feab.ASSEMBLY_ORDERED)
+    run_steps(P, n, 2, 4)
+    assert rel_l2(P.get_state(0), F.get_state(0)) > 1e-5       # the reference-parity answer differs
+
+
+@pytest.mark.parametrize("eq", [0, 3])
+def test_loop_modes_and_reruns_are_bitwise_identical(eq):
+    """Device-side WHILE graph vs host-batched loop, and run-to-run: identical bits (deterministic reductions)."""
+    xyz, tri = meshes.icosphere(12)
+    ob = meshes.boundary_flags(len(xyz), tri)
+    outs = []
+    for loop_mode in (feab.LOOP_GRAPH_WHILE, feab.LOOP_HOST_BATCHED, feab.LOOP_GRAPH_WHILE):
+        F = make(64, xyz, tri, ob, 0, loop_mode=loop_mode, assembly=feab.ASSEMBLY_ORDERED)
+        run_steps(F, len(xyz), eq, 4)
+        outs.append((F.get_state(0).copy(), F.get_state(1).copy(), F.stats()["iterations"]))
+    for o in outs[1:]:
+        assert (o[0] == outs[0][0]).all() and (o[1] == outs[0][1]).all() and o[2] == outs[0][2]
+
+
+def test_multi_step_call_equals_single_steps_and_live_parameter_change():
+    xyz, tri = meshes.icosphere(10)
+    ob = meshes.boundary_flags(len(xyz), tri)
+    V = len(xyz)
+    v0 = np.zeros(V, np.float32)
+    v0[meshes.seed_nodes(V)] = 1.0
+    A, B = make(64, xyz, tri, ob, 0), make(64, xyz, tri, ob, 0)
+    D = O.Oracle(xyz, tri, ob, 0, real=64)
+    for X in (A, B, D):
+        X.set_equation(0)
+        X.set_values(v0)
+    A.step(5)                       # device-resident batch (benchmark mode)
+    for _ in range(5):
+        B.step(1)
+    assert (A.get_values() == B.get_values()).all()
+    D.step(5)
+    # the GUI may edit parameters between any two steps (src/Application.cpp:373-423): operator cache must notice
+    for X in (A, D):
+        X.set_params(0, 0.05, 0.2)
+        X.step(2)
+    assert rel_l2(A.get_state(0), D.get_state(0)) <= FP64_STEP_TOL
+
+
+def test_zero_rhs_gray_scott_feed_dirichlet_and_instability():
+    xyz, tri = meshes.disk(7)
+    ob = meshes.boundary_flags(len(xyz), tri)
+    V = len(xyz)
+    F = make(64, xyz, tri, ob, 0)
+    for eq in (0, 1, 2):
+        F.clear()
+        F.set_equation(eq)
+        F.step(3)
+        assert (F.get_values() == 0).all() and F.stats()["iterations"][0] == 0
+    F.clear()
+    F.set_equation(3)
+    F.step(2)
+    assert (F.get_state(0) > 0).all() and (F.get_values() == 0).all()
+    F.clear()
+    F.set_equation(0)
+    F.set_values(np.full(V, 3.0, np.float32))
+    F.step(1)
+    v = F.get_values()
+    assert (v[ob == 1] == 0).all() and (v[ob == 0] > 0).all() and not F.unstable()
+    F.set_values(np.full(V, 5e4, np.float32))
+    F.step(1)
+    assert F.unstable()
+    F.set_values(np.full(V, -5e4, np.float32))
+    F.step(1)
+    assert not F.unstable()
+    F.clear()
+    assert not F.unstable() and (F.get_values() == 0).all()
+
+
+def test_brush_and_host_value_round_trip():
+    xyz, tri = meshes.icosphere(5)
+    ob = meshes.boundary_flags(len(xyz), tri)
+    V = len(xyz)
+    F = make(64, xyz, tri, ob, 0)
+    F.brush(meshes.seed_nodes(V), 1.0)
+    want = np.zeros(V, np.float32)
+    want[meshes.seed_nodes(V)] = 1.0
+    assert (F.get_values() == want).all()
+    D = O.Oracle(xyz, tri, ob, 0, real=64)
+    D.set_equation(0)
+    D.set_values(want)
+    D.step(1)
+    F.set_equation(0)
+    host = want.copy()
+    F.step(1, values=host, sync_values=True)     # the reference's data contract through surface->values
+    assert rel_l2(host, D.get_values()) <= FP64_STEP_TOL
+
+
+def test_reference_interface_mirror():
+    """Code written against the reference's classes runs unchanged against the mirror (femlib)."""
+    from fea_visualizer_b200 import BoundaryCondition, CUDASolver, Equation, FEMContext, Surface
+    xyz, tri = meshes.disk(6)
+    surface = Surface.from_arrays(xyz, tri)
+    fem_ctx = FEMContext(real=64)
+    assert fem_ctx.equation == Equation.Wave and fem_ctx.boundary_condition == BoundaryCondition.Dirichlet
+    solver = CUDASolver(fem_ctx)
+    fem_ctx.init_from_surface(surface)
+    solver.clear_values()
+    assert fem_ctx.num_nodes() == len(xyz) and fem_ctx.num_unknowns() == len(xyz) - surface.num_boundary_points
+    assert fem_ctx.num_max_nonzeros_per_row() == 7
+    D = O.Oracle(xyz, tri, surface.on_boundary, 0, real=64)
+    for eq in (Equation.Heat, Equation.Wave, Equation.Advection_Diffusion, Equation.Reaction_Diffusion):
+        fem_ctx.equation = eq
+        D.set_equation(int(eq))
+        solver.clear_values()
+        surface.clear_values()
+        D.clear()
+        surface.values[meshes.seed_nodes(len(xyz))] = 1.0
+        D.set_values(surface.values)
+        for _ in range(3):
+            solver.advance_time()
+            D.step(1)
+            assert not solver.has_numerical_instability()
+        assert rel_l2(surface.values, D.get_values()) <= 1e-7
+    fem_ctx.boundary_condition = BoundaryCondition.Neumann
+    fem_ctx.update_boundary_conditions()
+    assert fem_ctx.num_unknowns() == len(xyz) and (fem_ctx.idx_map == np.arange(len(xyz))).all()
+
+
+# ---------------------------------------------------------------------------------------------- full-size properties
+def test_c3_wave_1m_vertices_properties():
+    """BASELINE.json configs[2] size (icosphere nu=316, 998 562 vertices): size-independent properties."""
+    nu = 316
+    xyz, tri = meshes.icosphere(nu)
+    V = len(xyz)
+    F = make(64, xyz, tri, np.zeros(V, np.uint8), 0)
+    Vc, n, nnz, max_row = F.counts()
+    assert (n, nnz, max_row) == (998562, 7 * V - 12, 7)
+    rowptr, col, M = F.csr(0)
+    assert (np.diff(rowptr) >= 6).all() and (col[rowptr[:-1]] <= np.arange(n)).all()
+    assert abs(M.sum() - 4 * np.pi) < 1e-3                       # total mass = area of the unit sphere
+    K = F.csr(1)[2]
+    rs = np.add.reduceat(K, rowptr[:-1])
+    assert np.abs(rs).max() < 1e-9                               # stiffness rows sum to zero
+    # heat: mass is conserved on a closed surface: 1^T M u is invariant under (M/dt + kK) u+ = (M/dt) u
+    F.set_equation(0)
+    v0 = np.zeros(V, np.float32)
+    v0[meshes.seed_nodes(V)] = 1.0
+    F.set_values(v0)
+    lumped = np.add.reduceat(M, rowptr[:-1])
+    m0 = float(lumped @ v0.astype(np.float64))
+    F.step(1)
+    assert abs(float(lumped @ F.get_state(0)) - m0) <= 1e-10 * abs(m0)
+    F.step(2)                                                    # values pass through float between steps
+    assert abs(float(lumped @ F.get_state(0)) - m0) <= 1e-6 * abs(m0)
+    st = F.stats()
+    assert st["rel_residual"][0] < 2.3e-16 and 0 < st["iterations"][0] < 2000
+    # wave: three steps stay finite, the solver reports convergence
+    F.clear()
+    F.set_equation(1)
+    F.set_values(v0)
+    F.step(3)
+    assert np.isfinite(F.get_values()).all() and not F.unstable()
+    assert F.stats()["rel_residual"][0] < 2.3e-16
