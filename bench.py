@@ -94,8 +94,11 @@ class ClockSampler:
 
 
 def build_mesh(nu):
+    """Icosphere with the element size of the reference's bundled icosphere.obj (radius = nu / 32): on the unit
+    sphere the reference's own Gray-Scott step (reaction terms not mass-weighted, CPUSolver.cpp:134,137) reports
+    has_numerical_instability() within 5 steps from ~1e5 vertices on."""
     from fea_visualizer_b200 import meshes
-    xyz, tri = meshes.icosphere(nu)
+    xyz, tri = meshes.icosphere(nu, radius=nu / 32.0)
     ob = np.zeros(len(xyz), dtype=np.uint8)   # closed surface: no boundary nodes (checked by tests/test_meshes.py)
     return xyz, tri, ob
 
@@ -113,9 +116,9 @@ def seed_protocol(F, V, nsteps):
 # ------------------------------------------------------------------------------------------------ CPU reference
 def cpu_reference(sample_nu, steps, warmup, threads, target_rows=None):
     """Times the UNMODIFIED reference (Eigen fp32 Jacobi-PCG, oracle/_ref/libfea_ref_fast.so) on a bounded sample of
-    the workload: the same Gray-Scott protocol on a smaller icosphere from the same generator.  Returns steps/s of the
-    sample and the figure converted to the target mesh by rows x iterations (iterations ~ sqrt(rows), measured
-    scaling recorded in BASELINE.md)."""
+    the workload: the same Gray-Scott protocol on a smaller icosphere from the same generator with the same element
+    size (so the PCG iteration counts are those of the full mesh).  Returns steps/s of the sample and the figure
+    converted to the target mesh by the row ratio."""
     from fea_visualizer_b200 import meshes
     from oracle import oracle as O
     fast = O.reference_available(fast=True)
@@ -147,9 +150,9 @@ def cpu_reference(sample_nu, steps, warmup, threads, target_rows=None):
     out = {"sample_steps_per_s": sps, "sample_rows": V, "assembly_s": t_asm, "cores": used, "kind": "reference",
            "build": "fast(-O3 -march=x86-64-v3 -fopenmp)" if fast else "pin(-O2)"}
     if target_rows:
-        ratio = (target_rows / V) ** 1.5     # rows x iterations, iterations ~ sqrt(rows) at fixed dt
+        ratio = target_rows / V              # same element size and dt => same PCG iteration counts; work ~ rows
         out["converted_steps_per_s"] = sps / ratio
-        out["conversion"] = f"(rows_target/rows_sample)^1.5 = {ratio:.2f}"
+        out["conversion"] = f"rows_target/rows_sample = {ratio:.3f}"
     return out
 
 
@@ -172,7 +175,8 @@ def main():
     world = env_int("WORLD_SIZE", 1)
     local_rank = env_int("LOCAL_RANK", 0)
     V_target = 10 * args.nu * args.nu + 2
-    workload = f"gray-scott icosphere nu={args.nu} ({V_target} vertices, {20 * args.nu * args.nu} triangles), reference default parameters"
+    workload = (f"gray-scott icosphere nu={args.nu} radius={args.nu / 32.0:g} ({V_target} vertices, {20 * args.nu * args.nu} triangles), "
+                "reference default parameters")
     ncores = os.cpu_count() or 1
 
     if args.impl == "reference":

@@ -22,7 +22,7 @@ _ICO_F = np.array(
      [4, 9, 5], [2, 4, 11], [6, 2, 10], [8, 6, 7], [9, 8, 1]], dtype=np.int64)
 
 
-def icosphere(nu: int, displace: bool = False):
+def icosphere(nu: int, displace: bool = False, radius: float = 1.0):
     """Class-I geodesic subdivision of the icosahedron: every face split into nu^2 triangles,
     vertices normalised to radius 1 and rounded to float32 (the reference's storage type).
 
@@ -31,6 +31,9 @@ def icosphere(nu: int, displace: bool = False):
     first appearance over faces, stored low->high vertex), then the face-interior points of each of
     the 20 faces by face id, row-major in the face's barycentric grid.  ``displace`` applies the
     "bunny surrogate" radial displacement r = 1 + 0.15 sin(3x) sin(4y) sin(5z).
+    ``radius`` scales the sphere (in float64, before the float32 rounding): radius = nu / 32 keeps the element
+    size of the reference's bundled icosphere.obj (nu = 32, radius 1) at any vertex count, which is what keeps
+    the reference's non-mass-weighted Gray-Scott reaction terms stable on large meshes.
     """
     nu = int(nu)
     assert nu >= 1
@@ -98,6 +101,8 @@ def icosphere(nu: int, displace: bool = False):
     if displace:
         r = 1.0 + 0.15 * np.sin(3 * pos[:, 0]) * np.sin(4 * pos[:, 1]) * np.sin(5 * pos[:, 2])
         pos *= r[:, None]
+    if radius != 1.0:
+        pos *= float(radius)
     assert tri.min() >= 0 and tri.shape[0] == 20 * nu * nu
     return np.ascontiguousarray(pos, dtype=np.float32), np.ascontiguousarray(tri, dtype=np.uint32)
 

@@ -98,8 +98,9 @@ def test_bundled_meshes_sizes():
         sizes = g[f"{name}/bc{bc}/sizes"]
         assert (n, max_row, nnz) == (sizes[0], sizes[1], sizes[2])
         assert len(F.csr(2)[1]) == sizes[4]
-        for w in range(3):
-            assert abs(F.csr(w)[2].sum() - g[f"{name}/bc{bc}/sums"][w]) <= 2e-5 * max(1.0, abs(g[f"{name}/bc{bc}/sums"][w]))
+        for w in range(3):   # checksum of all entries vs the fp32 reference's (scale: sum of magnitudes)
+            val = F.csr(w)[2]
+            assert abs(val.sum() - g[f"{name}/bc{bc}/sums"][w]) <= 1e-6 * np.abs(val).sum()
 
 
 def test_velocity_change_reassembles_and_bc_switch():
