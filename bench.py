@@ -168,6 +168,7 @@ def main():
     ap.add_argument("--cpu-nu", type=int, default=env_int("FEAB_BENCH_CPU_NU", 316))
     ap.add_argument("--cpu-steps", type=int, default=3)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--loop", default="graph", choices=["graph", "host"], help="solve-loop driver: device-side WHILE graph or host-batched")
     ap.add_argument("--tol", type=float, default=-1.0, help="<0: epsilon of the arithmetic type (Eigen default)")
     args = ap.parse_args()
 
@@ -218,6 +219,8 @@ def main():
     F = feab.Feab(real=args.real, device=local_rank)
     if args.tol >= 0:
         F.set_solver(tolerance=args.tol)
+    if args.loop == "host":
+        F.set_solver(loop_mode=feab.LOOP_HOST_BATCHED)
     t0 = time.perf_counter()
     F.set_mesh(xyz, tri, ob)
     setup_s = time.perf_counter() - t0

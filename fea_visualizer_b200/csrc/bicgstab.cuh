@@ -42,7 +42,7 @@ struct BicgGrid {
 // partial layout inside `part` (each g_part long):
 //  0: |r|^2   1: r0.r   2: r0.v   3: v.v   4: t.s   5: t.t   6: restart |r|^2
 template <typename R>
-__device__ __forceinline__ R* bpart(R* part, int which, int g_part) {
+__host__ __device__ __forceinline__ R* bpart(R* part, int which, int g_part) {
     return part + (size_t)which * g_part;
 }
 
@@ -288,15 +288,23 @@ void bicg_iteration(cudaStream_t s, const int* rowptr, const int* col, const R* 
     const int np_vec = g.g_vec, np_tile = g.g_tile;
     // restart pair (no-ops unless restart_now)
     spmv_plain<R><<<g.g_tile, kBlock, smem, s>>>(rowptr, col, A, bv.x, bv.t, (const R*)nullptr, n, g.num_tiles, st, 1, (R*)nullptr, (R*)nullptr);
+    DBG(s, "bicg_iteration: restart_spmv");
     bicg_restart_vec<R><<<g.g_vec, kBlock, 0, s>>>(bv, n, st, part, g.g_part);
+    DBG(s, "bicg_iteration: restart_vec");
     bicg_p<R><<<g.g_vec, kBlock, 0, s>>>(bv, n, st, part, g.g_part, np_vec);
+    DBG(s, "bicg_iteration: bicg_p");
     spmv_plain<R><<<g.g_tile, kBlock, smem, s>>>(rowptr, col, A, bv.y, bv.v, bv.r0, n, g.num_tiles, st, 0, bpart(part, 2, g.g_part),
                                                  bpart(part, 3, g.g_part));
+    DBG(s, "bicg_iteration: spmv1");
     bicg_s<R><<<g.g_vec, kBlock, 0, s>>>(bv, n, st, part, g.g_part, np_tile);
+    DBG(s, "bicg_iteration: bicg_s");
     spmv_plain<R><<<g.g_tile, kBlock, smem, s>>>(rowptr, col, A, bv.z, bv.t, bv.s, n, g.num_tiles, st, 0, bpart(part, 2, g.g_part),
                                                  bpart(part, 3, g.g_part));
+    DBG(s, "bicg_iteration: spmv2");
     bicg_x<R><<<g.g_vec, kBlock, 0, s>>>(bv, n, st, part, g.g_part, np_tile);
+    DBG(s, "bicg_iteration: bicg_x");
     bicg_end<R><<<1, kBlock, 0, s>>>(st, part, g.g_part, np_vec, cond, use_cond);
+    DBG(s, "bicg_iteration: bicg_end");
 }
 
 }  // namespace feab

@@ -4,10 +4,27 @@
 #include <cfloat>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 
 namespace feab {
 
 constexpr int kBlock = 256;  // threads per CTA for every streaming kernel
+
+// FEAB_DEBUG=1: synchronise and report after instrumented launches (debug aid, off by default)
+static inline bool dbg_on() {
+    static int v = -1;
+    if (v < 0) v = getenv("FEAB_DEBUG") ? 1 : 0;
+    return v == 1;
+}
+#define DBG(stream, ...)                                  \
+    do {                                                  \
+        if (dbg_on()) {                                   \
+            cudaError_t e_ = cudaStreamSynchronize(stream); \
+            fprintf(stderr, "[feab] " __VA_ARGS__);       \
+            fprintf(stderr, " -> %s\n", cudaGetErrorString(e_)); \
+            fflush(stderr);                               \
+        }                                                 \
+    } while (0)
 
 // Correctly-rounded primitives that nvcc never contracts into FMAs, so that the per-element arithmetic
 // follows the reference's operation order exactly (the oracle is built with -ffp-contract=off).

@@ -5,6 +5,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <string>
@@ -58,6 +59,7 @@ struct DevBuf {
 };
 
 static inline int cdiv64(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
+
 
 struct SolverBase {
     virtual ~SolverBase() {}
@@ -857,13 +859,19 @@ void SolverT<R>::enqueue_bicgstab(const R* A, const R* dinv, R* x, bool capturin
         CK(cudaStreamEndCapture(stream2_, nullptr));
     } else {
         cudaGraphConditionalHandle none = 0;
+        DBG(stream_, "bicg: before begin n=%lld g_vec=%d g_tile=%d g_part=%d", (long long)n_, g_vec_, g_tile_, g_part_);
         bicg_begin<R><<<g_vec_, kBlock, 0, stream_>>>(bv, n_, part, g_part_);
+        DBG(stream_, "bicg: begin");
         bicg_begin2<R><<<1, kBlock, 0, stream_>>>(d_bst_, part, g_vec_, tol(), maxit(), none, 0);
+        DBG(stream_, "bicg: begin2");
         launches_ += 2;
         const int batch = 4;
         const int64_t mi = maxit();
         for (int64_t trips = 0; trips < 2 * mi + batch;) {
-            for (int b = 0; b < batch; b++) bicg_iteration<R>(stream_, d_rowptr_.p, d_col_.p, A, bv, n_, bg, d_bst_, part, sm1, none, 0);
+            for (int b = 0; b < batch; b++) {
+                bicg_iteration<R>(stream_, d_rowptr_.p, d_col_.p, A, bv, n_, bg, d_bst_, part, sm1, none, 0);
+                DBG(stream_, "bicg: iteration trips=%lld b=%d", (long long)trips, b);
+            }
             launches_ += (int64_t)kBicgKernelsPerIter * batch;
             trips += batch;
             CK(cudaMemcpyAsync(h_flag_, &d_bst_->done, sizeof(int), cudaMemcpyDeviceToHost, stream_));
