@@ -16,6 +16,7 @@
 #include "common.cuh"
 #include "pattern.cuh"
 #include "solver.cuh"
+#include "spmv_tma.cuh"
 
 namespace feab {
 
@@ -52,7 +53,8 @@ struct DevBuf {
         if (n == count && p) return;
         release();
         if (n == 0) n = 1;
-        cudaError_t e = cudaMalloc(&p, n * sizeof(T));
+        // kTmaPad spare elements: 1-D bulk TMA copies round their sizes up to 16 bytes
+        cudaError_t e = cudaMalloc(&p, (n + kTmaPad) * sizeof(T));
         if (e != cudaSuccess) throw Err{FEAB_ENOMEM, std::string("cudaMalloc of ") + std::to_string(n * sizeof(T)) + " bytes: " + cudaGetErrorString(e)};
         count = n;
     }
@@ -123,6 +125,57 @@ class SolverT final : public SolverBase {
         CK(cudaMalloc(&d_bst_, sizeof(BicgState<R>)));
         CK(cudaMemset(d_bst_, 0, sizeof(BicgState<R>)));
         d_scan_total_.alloc(1);
+        if (const char* v = getenv("FEAB_SPMV")) spmv_variant_ = atoi(v);
+        if (const char* v = getenv("FEAB_PREFETCH_X")) prefetch_x_ = atoi(v);
+        setup_spmv_variants();
+    }
+
+    // ---- SpMV variants: 0 = LDG/CSR-stream (solver.cuh), 1.. = TMA pipelines (spmv_tma.cuh) ----
+    template <int ROWS, int CPR, int STAGES, int MINB>
+    void setup_tma() {
+        using Cfg = TmaCfg<R, ROWS, CPR, STAGES>;
+        CK(cudaFuncSetAttribute(spmv_dot_tma<R, ROWS, CPR, STAGES, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::kSmemBytes));
+    }
+    void setup_spmv_variants() {
+        setup_tma<256, 10, 3, 2>();
+        setup_tma<512, 9, 3, 1>();
+        setup_tma<256, 10, 2, 3>();
+        setup_tma<512, 8, 2, 2>();
+        setup_tma<1024, 8, 2, 1>();
+    }
+    template <int ROWS, int CPR, int STAGES, int MINB>
+    void launch_tma(cudaStream_t s, const R* A, const R* x, R* y, CgState<R>* st) {
+        using Cfg = TmaCfg<R, ROWS, CPR, STAGES>;
+        const int tiles = std::max(1, cdiv64(n_, ROWS));
+        const int grid = std::min(tiles, sms_ * MINB);
+        spmv_dot_tma<R, ROWS, CPR, STAGES, MINB><<<grid, ROWS, Cfg::kSmemBytes, s>>>(d_rowptr_.p, d_col_.p, A, x, y, n_, tiles, st, part_pap(), prefetch_x_);
+    }
+    template <int ROWS, int MINB>
+    int grid_tma() const {
+        return std::min(std::max(1, cdiv64(n_, ROWS)), sms_ * MINB);
+    }
+    // number of p.Ap partials the SpMV of the current variant writes
+    int spmv_parts() const {
+        switch (spmv_variant_) {
+            case 1: return grid_tma<256, 2>();
+            case 2: return grid_tma<512, 1>();
+            case 3: return grid_tma<256, 3>();
+            case 4: return grid_tma<512, 2>();
+            case 5: return grid_tma<1024, 1>();
+            default: return g_tile_;
+        }
+    }
+    void launch_spmv(cudaStream_t s, const R* A, const R* x, R* y, CgState<R>* st) {
+        switch (spmv_variant_) {
+            case 1: launch_tma<256, 10, 3, 2>(s, A, x, y, st); break;
+            case 2: launch_tma<512, 9, 3, 1>(s, A, x, y, st); break;
+            case 3: launch_tma<256, 10, 2, 3>(s, A, x, y, st); break;
+            case 4: launch_tma<512, 8, 2, 2>(s, A, x, y, st); break;
+            case 5: launch_tma<1024, 8, 2, 1>(s, A, x, y, st); break;
+            default:
+                spmv_dot<R><<<g_tile_, kBlock, kTileCap * sizeof(R), s>>>(d_rowptr_.p, d_col_.p, A, x, y, n_, num_tiles_, st, part_pap());
+                break;
+        }
     }
     ~SolverT() override {
         cudaSetDevice(device_);
@@ -272,7 +325,7 @@ class SolverT final : public SolverBase {
         num_tiles_ = std::max(1, cdiv64(n, kTileRows));
         g_tile_ = std::min(num_tiles_, sms_ * 8);
         g_vec_ = std::max(1, std::min(cdiv64(std::max<int64_t>(n / Vec<R>::N, 1), kBlock), sms_ * 8));
-        g_part_ = std::max(g_tile_, g_vec_);
+        g_part_ = std::max(std::max(g_tile_, g_vec_), sms_ * 8);
         d_part_.alloc((size_t)16 * g_part_);
         resize_state();
     }
@@ -487,8 +540,8 @@ class SolverT final : public SolverBase {
 
     void launch_iteration(cudaStream_t s, int slot, const R* A, const R* dinv, R* x, cudaGraphConditionalHandle cond, int use_cond) {
         CgState<R>* st = d_st_ + slot;
-        spmv_dot<R><<<g_tile_, kBlock, kTileCap * sizeof(R), s>>>(d_rowptr_.p, d_col_.p, A, d_p_[slot].p, d_y_.p, n_, num_tiles_, st, part_pap());
-        cg_update<R><<<g_vec_, kBlock, 0, s>>>(x, d_r_[slot].p, d_p_[slot].p, d_y_.p, dinv, n_, st, part_pap(), g_tile_, part_rr(), part_rz());
+        launch_spmv(s, A, d_p_[slot].p, d_y_.p, st);
+        cg_update<R><<<g_vec_, kBlock, 0, s>>>(x, d_r_[slot].p, d_p_[slot].p, d_y_.p, dinv, n_, st, part_pap(), spmv_parts(), part_rr(), part_rz());
         cg_direction<R><<<g_vec_, kBlock, 0, s>>>(d_r_[slot].p, d_p_[slot].p, dinv, n_, st, part_rr(), part_rz(), g_vec_, cond, use_cond);
     }
 
@@ -694,23 +747,27 @@ class SolverT final : public SolverBase {
         // make the loop state "running" with harmless scalars
         CgState<R> h;
         std::memset(&h, 0, sizeof(h));
-        h.abs_new[0] = h.abs_new[1] = (R)0;  // alpha = 0: x, r unchanged
+        h.abs_new[0] = h.abs_new[1] = (R)1;
         h.thr = (R)0;
         h.iter1 = 1;
         h.maxit = INT32_MAX - 4;
         CK(cudaMemcpy(d_st_, &h, sizeof(h), cudaMemcpyHostToDevice));
-        std::vector<R> ones(g_part_ * 3, (R)1);
-        CK(cudaMemcpy(d_part_.p, ones.data(), ones.size() * sizeof(R), cudaMemcpyHostToDevice));
+        // p.Ap partials huge -> alpha ~ 0 (x, r unchanged); |r|^2 partials 1 -> not converged; r.z partials 0 -> beta = 0
+        std::vector<R> init((size_t)g_part_ * 3, (R)0);
+        for (int i = 0; i < g_part_; i++) {
+            init[i] = Ops<R>::huge() / (R)(4 * g_part_);
+            init[(size_t)g_part_ + i] = (R)1;
+        }
+        CK(cudaMemcpy(d_part_.p, init.data(), init.size() * sizeof(R), cudaMemcpyHostToDevice));
         const StepScalars sc = scalars();
         cudaGraphConditionalHandle none = 0;
         auto launch = [&]() {
             switch (kernel) {
                 case 0:
-                    spmv_dot<R><<<g_tile_, kBlock, kTileCap * sizeof(R), stream_>>>(d_rowptr_.p, d_col_.p, d_A0_.p, d_p_[0].p, d_y_.p, n_, num_tiles_,
-                                                                                    nullptr, part_pap());
+                    launch_spmv(stream_, d_A0_.p, d_p_[0].p, d_y_.p, nullptr);
                     break;
                 case 1:
-                    cg_update<R><<<g_vec_, kBlock, 0, stream_>>>(d_w_[0].p, d_r_[0].p, d_p_[0].p, d_y_.p, d_dinv0_.p, n_, d_st_, part_pap(), g_tile_,
+                    cg_update<R><<<g_vec_, kBlock, 0, stream_>>>(d_w_[0].p, d_r_[0].p, d_p_[0].p, d_y_.p, d_dinv0_.p, n_, d_st_, part_pap(), spmv_parts(),
                                                                  part_rr(), part_rz());
                     break;
                 case 2:
@@ -795,6 +852,7 @@ class SolverT final : public SolverBase {
     int* d_unstable_ = nullptr;
 
     int num_tiles_ = 1, g_tile_ = 1, g_vec_ = 1, g_part_ = 1;
+    int spmv_variant_ = 0, prefetch_x_ = 0;
     bool op_valid_ = false;
     int op_eq_ = -1, op_transposed_ = 0;
     FeabParams op_par_{};
