@@ -37,6 +37,19 @@ def env_int(name, default):
         return default
 
 
+def ncu_traffic(rows, dtype):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from the committed ncu --set full
+    capture of the same workload (profiles/r01_spmv_traffic.json); None when the workload differs."""
+    p = os.path.join(ROOT, "profiles", "r01_spmv_traffic.json")
+    try:
+        t = json.load(open(p))
+        if t["rows"] == rows and t["dtype"] == dtype:
+            return t["traffic_bytes_per_launch"]
+    except Exception:
+        pass
+    return None
+
+
 def measured_peak():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -279,7 +292,8 @@ def main():
         it_ms = kernels["spmv_dot"]["ms"] + kernels["cg_update"]["ms"] + kernels["cg_direction"]["ms"]
         it_bytes = sum(kernels[k]["algorithmic_bytes"] for k in ("spmv_dot", "cg_update", "cg_direction"))
         roof = {"bound": "hbm", "kernel": "spmv_dot", "achieved": k0["GBps"], "peak": peak, "unit": "GB/s", "frac": k0["GBps"] / peak,
-                "traffic": None, "peak_source": peak_src, "frac_of_nominal_8TBps": k0["GBps"] / 8000.0,
+                "traffic": ncu_traffic(n, "f64" if args.real == 64 else "f32"), "algorithmic_bytes": k0["algorithmic_bytes"],
+                "traffic_source": "profiles/r01_spmv_traffic.json (ncu --set full, per launch)", "peak_source": peak_src, "frac_of_nominal_8TBps": k0["GBps"] / 8000.0,
                 "pcg_iteration": {"ms": it_ms, "algorithmic_bytes": it_bytes, "GBps": it_bytes / it_ms / 1e6,
                                   "frac": it_bytes / it_ms / 1e6 / peak},
                 "kernels": kernels}

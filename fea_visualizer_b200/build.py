@@ -9,7 +9,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libfeab.so")
 SOURCES = ["feab.cu"]
-HEADERS = ["common.cuh", "pattern.cuh", "assembly.cuh", "solver.cuh", "bicgstab.cuh", os.path.join("..", "..", "include", "feab.h")]
+HEADERS = ["common.cuh", "pattern.cuh", "assembly.cuh", "solver.cuh", "bicgstab.cuh", "spmv_tma.cuh", os.path.join("..", "..", "include", "feab.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC", "-shared"]
 
 

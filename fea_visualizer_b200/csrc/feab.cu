@@ -852,7 +852,7 @@ class SolverT final : public SolverBase {
     int* d_unstable_ = nullptr;
 
     int num_tiles_ = 1, g_tile_ = 1, g_vec_ = 1, g_part_ = 1;
-    int spmv_variant_ = 0, prefetch_x_ = 0;
+    int spmv_variant_ = 4, prefetch_x_ = 0;  // 4 = TMA pipeline, 512-row tiles, 2 stages, 2 CTAs/SM (profiles/r01_spmv_sweep.txt)
     bool op_valid_ = false;
     int op_eq_ = -1, op_transposed_ = 0;
     FeabParams op_par_{};
