@@ -107,7 +107,7 @@ template <typename R>
 __global__ void __launch_bounds__(kBlock) assemble_scatter(const float* __restrict__ xyz, const uint32_t* __restrict__ tri, int64_t T,
                                                             const uint8_t* __restrict__ on_boundary, const int* __restrict__ smap,
                                                             R vx, R vy, R vz, R* __restrict__ Mv, R* __restrict__ Kv,
-                                                            R* __restrict__ Av) {
+                                                            R* __restrict__ Av, R* __restrict__ AvT) {
     using O = Ops<R>;
     int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= T) return;
@@ -140,7 +140,10 @@ __global__ void __launch_bounds__(kBlock) assemble_scatter(const float* __restri
             if (p < 0) continue;
             atomicAdd(&Kv[p], O::mul(e.area, edot3(e.G[i], e.G[j])));
             atomicAdd(&Mv[p], O::mul(ms, (R)(i == j ? 2 : 1)));
-            if (interior[i] && interior[j]) atomicAdd(&Av[p], adv[j]);
+            if (interior[i] && interior[j]) {
+                atomicAdd(&Av[p], adv[j]);
+                atomicAdd(&AvT[p], adv[i]);  // slot (i, j) of Adv^T holds Adv(j, i) = adv[i]
+            }
         }
 }
 
@@ -150,10 +153,11 @@ __global__ void __launch_bounds__(kBlock) assemble_scatter(const float* __restri
 // same real type) bit-identical to the CPU oracle.  No atomics, no zero-fill needed.
 template <typename R>
 __global__ void __launch_bounds__(kBlock) assemble_ordered(const float* __restrict__ xyz, const uint32_t* __restrict__ tri, int64_t n,
-                                                            const uint8_t* __restrict__ on_boundary, const int* __restrict__ idx_map,
+                                                            const uint8_t* __restrict__ on_boundary, const int* __restrict__ colmap,
                                                             const int* __restrict__ cptr, const int* __restrict__ corner,
                                                             const int* __restrict__ rowptr, const int* __restrict__ col, R vx, R vy,
-                                                            R vz, R* __restrict__ Mv, R* __restrict__ Kv, R* __restrict__ Av) {
+                                                            R vz, R* __restrict__ Mv, R* __restrict__ Kv, R* __restrict__ Av,
+                                                            R* __restrict__ AvT) {
     using O = Ops<R>;
     int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= n) return;
@@ -162,6 +166,7 @@ __global__ void __launch_bounds__(kBlock) assemble_ordered(const float* __restri
         Mv[p] = (R)0;
         Kv[p] = (R)0;
         Av[p] = (R)0;
+        AvT[p] = (R)0;
     }
     R vel[3] = {vx, vy, vz};
     for (int q = cptr[r]; q < cptr[r + 1]; q++) {
@@ -178,7 +183,7 @@ __global__ void __launch_bounds__(kBlock) assemble_ordered(const float* __restri
         bool inti = !on_boundary[nd[i]];
 #pragma unroll
         for (int j = 0; j < 3; j++) {
-            int mj = idx_map[nd[j]];
+            int mj = colmap[nd[j]];
             if (mj < 0) continue;
             int p = rb;
             while (p < re && col[p] != mj) p++;  // rows are short (about 7 entries)
@@ -186,7 +191,12 @@ __global__ void __launch_bounds__(kBlock) assemble_ordered(const float* __restri
             // first contribution is stored, later ones added (0 + x is exact, so plain accumulation is identical)
             Kv[p] = O::add(Kv[p], O::mul(e.area, edot3(e.G[i], e.G[j])));
             Mv[p] = O::add(Mv[p], O::mul(ms, (R)(i == j ? 2 : 1)));
-            if (inti && !on_boundary[nd[j]]) Av[p] = O::add(Av[p], O::mul(as, edot3(tv, e.G[j])));
+            if (inti && !on_boundary[nd[j]]) {
+                Av[p] = O::add(Av[p], O::mul(as, edot3(tv, e.G[j])));
+                // Adv^T(row, col) = Adv(col, row): the same triangles in the same ascending order contribute
+                // Adv_loc(j, i), which depends only on its column index i (FEMContext.cpp:192)
+                AvT[p] = O::add(AvT[p], O::mul(as, edot3(tv, e.G[i])));
+            }
         }
     }
 }

@@ -1,0 +1,273 @@
+// Multi-GPU plumbing of the partitioned solver: scalar all-reduces and halo pushes done by the
+// solver's own kernels through peer memory over NVLink / NVSwitch -- no host round trip, no separate collective
+// launch.  Every rank (one process per GPU, or one "virtual rank" per handle in the single-process test driver)
+// owns one arena allocation that starts with a CommCtrl block; peers map the arena (cudaIpc or same-process
+// pointers) and write into it:
+//   * all-reduce: the last CTA of a producer kernel sums the kernel's per-CTA partials in a fixed order and
+//     stores the rank total + a sequence number into slot[seq & 1][rank] of EVERY rank's CommCtrl; the consumer
+//     kernel spins on its own (local) slots and adds the totals in rank order -> every rank obtains bit-identical
+//     sums, so all ranks take identical convergence decisions without talking to the host.
+//   * halo: a push kernel stores the boundary rows of a vector straight into the ghost tail of each neighbour's
+//     vector, then raises that neighbour's flag; the neighbour's SpMV waits for the flag only before its first
+//     boundary tile, so the interior rows overlap the transfer.
+// Double buffering by sequence parity is sufficient: a rank can publish all-reduce s+2 only after it consumed
+// s+1, which needs every peer's s+1, which each peer publishes after consuming s.
+// All spins are bounded (kSpinTimeoutNs): on timeout the kernel records an error and carries on, the host reports it.
+#pragma once
+#include "common.cuh"
+
+namespace feab {
+
+constexpr int kMaxRanks = 8;
+constexpr unsigned long long kSpinTimeoutNs = 10ull * 1000 * 1000 * 1000;
+
+struct ArSlot {
+    double v[4];
+    unsigned long long seq;
+    unsigned long long pad[3];
+};
+struct CommCtrl {  // written by peers
+    ArSlot slot[2][kMaxRanks];
+    unsigned long long halo_flag[kMaxRanks];   // [source rank] number of direction-halo pushes received
+    unsigned long long state_flag[kMaxRanks];  // [source rank] number of end-of-step state pushes received
+    unsigned long long full_flag[kMaxRanks];   // [source rank] number of full value broadcasts received
+    unsigned long long pad[8];
+};
+struct CommLocal {  // private to the rank
+    unsigned long long ar_seq;
+    unsigned long long halo_seq, state_seq, full_seq;
+    unsigned int ticket;
+    int error;
+};
+constexpr size_t kCtrlBytes = (sizeof(CommCtrl) + 255) / 256 * 256;
+
+// Passed by value to kernels.  world == 1: nothing below is touched.
+struct Comm {
+    int rank = 0, world = 1;
+    CommCtrl* ctrl[kMaxRanks] = {};  // ctrl[rank] is local
+    CommLocal* loc = nullptr;
+};
+
+// Which neighbours receive which of my rows, and where they land in the neighbour's vectors.
+struct HaloPlan {
+    int nnb = 0;
+    int nb_rank[kMaxRanks] = {};
+    int send_off[kMaxRanks + 1] = {};   // ranges in send_rows / send_nodes
+    int dst_col[kMaxRanks] = {};        // first ghost column of my block on that neighbour
+    const int* send_rows = nullptr;     // my local rows, ascending global unknown id per neighbour
+    const int* send_nodes = nullptr;    // their mesh nodes
+    char* base[kMaxRanks] = {};         // neighbour arena base, indexed by RANK
+    unsigned long long off_vec[5][kMaxRanks] = {};  // byte offsets of p[0], p[1], u, v, values in that arena, by RANK
+};
+enum { kVecP0 = 0, kVecP1 = 1, kVecU = 2, kVecV = 3, kVecValues = 4 };
+
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ double ld_volatile_f64(const double* p) {
+    double v;
+    asm volatile("ld.volatile.global.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
+    return v;
+}
+
+// Spin until *flag >= want (one thread).  Returns false on timeout.
+__device__ __forceinline__ bool spin_until_ge(const unsigned long long* flag, unsigned long long want, CommLocal* loc) {
+    if (ld_acquire_sys(flag) >= want) return true;
+    const unsigned long long t0 = globaltimer_ns();
+    while (ld_acquire_sys(flag) < want) {
+        __nanosleep(64);
+        if (globaltimer_ns() - t0 > kSpinTimeoutNs) {
+            loc->error = 1;
+            return false;
+        }
+    }
+    return true;
+}
+
+// Fixed-order sum of per-CTA partials written earlier IN THIS KERNEL by other CTAs (L2 loads, never the
+// non-coherent path).
+template <typename T, int NW>
+__device__ __forceinline__ T sum_partials_cg(const T* part, int count, T* sm) {
+    T s = T(0);
+    for (int i = threadIdx.x; i < count; i += blockDim.x) s += __ldcg(part + i);
+    T r = block_sum_n<T, NW>(s, sm);
+    __syncthreads();
+    return r;
+}
+
+// Producer side.  Call from ALL threads of EVERY CTA after thread 0 stored part[k * stride + blockIdx.x], k < K.
+// The last CTA to arrive publishes the rank totals to every rank.
+template <typename R, int K, int NW = kBlock / 32>
+__device__ __forceinline__ void ar_publish(const Comm& cm, const R* part, int stride, R* sm) {
+    __shared__ int s_last;
+    if (threadIdx.x == 0) {
+        __threadfence();
+        unsigned t = atomicAdd(&cm.loc->ticket, 1u);
+        s_last = (t == gridDim.x - 1) ? 1 : 0;
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    R tot[K];
+#pragma unroll
+    for (int k = 0; k < K; k++) tot[k] = sum_partials_cg<R, NW>(part + (size_t)k * stride, (int)gridDim.x, sm);
+    if (threadIdx.x == 0) {
+        cm.loc->ticket = 0;
+        const unsigned long long s = cm.loc->ar_seq + 1;
+        cm.loc->ar_seq = s;
+        for (int q = 0; q < cm.world; q++) {
+            ArSlot* sl = &cm.ctrl[q]->slot[s & 1][cm.rank];
+#pragma unroll
+            for (int k = 0; k < K; k++) sl->v[k] = (double)tot[k];
+        }
+        __threadfence_system();
+        for (int q = 0; q < cm.world; q++) st_release_sys(&cm.ctrl[q]->slot[s & 1][cm.rank].seq, s);
+    }
+}
+
+// Consumer side (the kernel launched after the producer on the same stream).  Every CTA calls it; result in all threads.
+template <typename R, int K>
+__device__ __forceinline__ void ar_consume(const Comm& cm, R (&out)[K]) {
+    __shared__ double s_v[4];
+    if (threadIdx.x == 0) {
+        const unsigned long long s = *(volatile unsigned long long*)&cm.loc->ar_seq;
+        const CommCtrl* me = cm.ctrl[cm.rank];
+        R acc[K];
+#pragma unroll
+        for (int k = 0; k < K; k++) acc[k] = (R)0;
+        for (int q = 0; q < cm.world; q++) {
+            const ArSlot* sl = &me->slot[s & 1][q];
+            spin_until_ge(&sl->seq, s, cm.loc);
+#pragma unroll
+            for (int k = 0; k < K; k++) acc[k] += (R)ld_volatile_f64(&sl->v[k]);
+        }
+#pragma unroll
+        for (int k = 0; k < K; k++) s_v[k] = (double)acc[k];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < K; k++) out[k] = (R)s_v[k];
+    __syncthreads();
+}
+
+// One CTA right after a producer: stores the all-reduced totals where single-CTA kernels (cg_begin) expect partials.
+template <typename R, int K>
+__global__ void ar_collect(Comm cm, R* __restrict__ totals) {
+    R t[K];
+    ar_consume<R, K>(cm, t);
+    if (threadIdx.x == 0)
+#pragma unroll
+        for (int k = 0; k < K; k++) totals[k] = t[k];
+}
+
+// Wait (one thread) until every neighbour's push number `want` has landed.  kind: 0 halo, 1 state, 2 full.
+__device__ __forceinline__ void wait_flags(const Comm& cm, const HaloPlan& hp, int kind, unsigned long long want) {
+    const CommCtrl* me = cm.ctrl[cm.rank];
+    if (kind == 2) {
+        for (int q = 0; q < cm.world; q++)
+            if (q != cm.rank) spin_until_ge(&me->full_flag[q], want, cm.loc);
+        return;
+    }
+    for (int i = 0; i < hp.nnb; i++) {
+        const int q = hp.nb_rank[i];
+        spin_until_ge(kind == 0 ? &me->halo_flag[q] : &me->state_flag[q], want, cm.loc);
+    }
+}
+__global__ void wait_kernel(Comm cm, HaloPlan hp, int kind) {
+    if (threadIdx.x == 0) {
+        const unsigned long long want = kind == 0 ? cm.loc->halo_seq : kind == 1 ? cm.loc->state_seq : cm.loc->full_seq;
+        wait_flags(cm, hp, kind, want);
+    }
+}
+
+// Push the boundary rows of up to two vectors (p of solve 0 / 1) into the neighbours' ghost tails, then raise
+// their halo flags.  One CTA: cuts of a surface mesh are O(sqrt(n)) rows.
+template <typename R>
+__global__ void __launch_bounds__(1024) halo_push(Comm cm, HaloPlan hp, const R* __restrict__ src0, int vec0, const R* __restrict__ src1,
+                                                  int vec1) {
+    for (int b = 0; b < hp.nnb; b++) {
+        const int q = hp.nb_rank[b];
+        const int beg = hp.send_off[b], cnt = hp.send_off[b + 1] - beg;
+        R* d0 = reinterpret_cast<R*>(hp.base[q] + hp.off_vec[vec0][q]) + hp.dst_col[b];
+        R* d1 = src1 ? reinterpret_cast<R*>(hp.base[q] + hp.off_vec[vec1][q]) + hp.dst_col[b] : nullptr;
+        for (int i = threadIdx.x; i < cnt; i += blockDim.x) {
+            const int row = hp.send_rows[beg + i];
+            d0[i] = src0[row];
+            if (src1) d1[i] = src1[row];
+        }
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned long long s = cm.loc->halo_seq + 1;
+        cm.loc->halo_seq = s;
+        for (int b = 0; b < hp.nnb; b++) st_release_sys(&cm.ctrl[hp.nb_rank[b]]->halo_flag[cm.rank], s);
+    }
+}
+
+// End of a time step: boundary rows of u and v (hidden solver state) and their surface values go to the neighbours.
+template <typename R>
+__global__ void __launch_bounds__(1024) state_push(Comm cm, HaloPlan hp, const R* __restrict__ u, const R* __restrict__ v,
+                                                   const float* __restrict__ values) {
+    for (int b = 0; b < hp.nnb; b++) {
+        const int q = hp.nb_rank[b];
+        const int beg = hp.send_off[b], cnt = hp.send_off[b + 1] - beg;
+        R* du = reinterpret_cast<R*>(hp.base[q] + hp.off_vec[kVecU][q]) + hp.dst_col[b];
+        R* dv = reinterpret_cast<R*>(hp.base[q] + hp.off_vec[kVecV][q]) + hp.dst_col[b];
+        float* dval = reinterpret_cast<float*>(hp.base[q] + hp.off_vec[kVecValues][q]);
+        for (int i = threadIdx.x; i < cnt; i += blockDim.x) {
+            const int row = hp.send_rows[beg + i];
+            const int node = hp.send_nodes[beg + i];
+            du[i] = u[row];
+            dv[i] = v[row];
+            dval[node] = values[node];
+        }
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned long long s = cm.loc->state_seq + 1;
+        cm.loc->state_seq = s;
+        for (int b = 0; b < hp.nnb; b++) st_release_sys(&cm.ctrl[hp.nb_rank[b]]->state_flag[cm.rank], s);
+    }
+}
+
+// surface->values is complete on every rank after advance_time() (the reference's data contract): each rank
+// broadcasts the values of the nodes it owns to all peers.  Grid-wide; the last CTA raises the flags.
+__global__ void __launch_bounds__(kBlock) values_broadcast(Comm cm, HaloPlan hp, const int* __restrict__ row_node, int64_t n_own,
+                                                           const float* __restrict__ values) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_own; i += (int64_t)gridDim.x * blockDim.x) {
+        const int node = row_node[i];
+        const float val = values[node];
+        for (int q = 0; q < cm.world; q++)
+            if (q != cm.rank) reinterpret_cast<float*>(hp.base[q] + hp.off_vec[kVecValues][q])[node] = val;
+    }
+    __threadfence_system();
+    __shared__ int s_last;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned t = atomicAdd(&cm.loc->ticket, 1u);
+        s_last = (t == gridDim.x - 1) ? 1 : 0;
+    }
+    __syncthreads();
+    if (s_last && threadIdx.x == 0) {
+        cm.loc->ticket = 0;
+        __threadfence_system();
+        const unsigned long long s = cm.loc->full_seq + 1;
+        cm.loc->full_seq = s;
+        for (int q = 0; q < cm.world; q++)
+            if (q != cm.rank) st_release_sys(&cm.ctrl[q]->full_flag[cm.rank], s);
+    }
+}
+
+}  // namespace feab

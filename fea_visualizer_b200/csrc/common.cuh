@@ -80,6 +80,22 @@ __device__ __forceinline__ T block_sum(T v, T* sm) {
     return r;
 }
 
+// Same for a CTA of NW warps (the TMA kernels use 512-thread CTAs).  `sm` must hold NW + 1 elements.
+template <typename T, int NW>
+__device__ __forceinline__ T block_sum_n(T v, T* sm /* NW + 1 */) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    v = warp_sum(v);
+    if (lane == 0) sm[w] = v;
+    __syncthreads();
+    if (w == 0) {
+        T t = lane < NW ? sm[lane] : T(0);
+        t = warp_sum(t);
+        if (lane == 0) sm[NW] = t;
+    }
+    __syncthreads();
+    return sm[NW];
+}
+
 // Deterministic grid-wide sum of `count` per-CTA partials, computed redundantly (and identically) by every
 // CTA of the consuming kernel: no atomics, no "last block" fence, no host round trip.
 template <typename T>

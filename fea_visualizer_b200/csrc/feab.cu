@@ -3,6 +3,8 @@
 // There is no CPU fallback: without a CUDA device feab_create fails with FEAB_ENOGPU.
 #include "../../include/feab.h"
 
+#include <unistd.h>
+
 #include <algorithm>
 #include <cmath>
 #include <cstdlib>
@@ -14,6 +16,7 @@
 #include "assembly.cuh"
 #include "bicgstab.cuh"
 #include "common.cuh"
+#include "partition.cuh"
 #include "pattern.cuh"
 #include "solver.cuh"
 #include "spmv_tma.cuh"
@@ -40,14 +43,22 @@ template <typename T>
 struct DevBuf {
     T* p = nullptr;
     size_t count = 0;
+    bool owner = true;
     DevBuf() = default;
     DevBuf(const DevBuf&) = delete;
     DevBuf& operator=(const DevBuf&) = delete;
     ~DevBuf() { release(); }
     void release() {
-        if (p) cudaFree(p);
+        if (p && owner) cudaFree(p);
         p = nullptr;
         count = 0;
+        owner = true;
+    }
+    void view(void* ptr, size_t n) {  // non-owning window into another allocation (the comm arena)
+        release();
+        p = static_cast<T*>(ptr);
+        count = n;
+        owner = false;
     }
     void alloc(size_t n) {
         if (n == count && p) return;
@@ -86,6 +97,21 @@ struct SolverBase {
     virtual void get_state(int which, void* out) = 0;
     virtual void set_state(int which, const void* in) = 0;
     virtual void time_kernel(int kernel, int reps, double* ms, double* bytes) = 0;
+    virtual void mg_config(int rank, int world) = 0;
+    virtual void mg_set_partition(const int32_t* part, int64_t V) = 0;
+    virtual void mg_export(FeabMgExport* out) = 0;
+    virtual void mg_connect(int peer, const FeabMgExport* e, int same_process) = 0;
+    virtual void mg_get_layout(int64_t* n_own, int64_t* n_int, int64_t* n_ghost, int64_t* n_cols) = 0;
+    virtual void mg_get_maps(int32_t* row_node, int32_t* col_unknown) = 0;
+    // lock-step driving (feab_mg_group_step)
+    enum { LS_PUSH_STATE, LS_BEGIN, LS_COLLECT, LS_CG_BEGIN, LS_SPMV, LS_UPDATE, LS_DIRECTION, LS_FINISH };
+    virtual cudaStream_t ls_prepare(cudaStream_t shared) = 0;
+    virtual void ls_phase(int phase, int slot) = 0;
+    virtual int ls_num_solves() = 0;
+    virtual int ls_poll_done(int slot) = 0;
+    virtual int64_t ls_maxit() = 0;
+    virtual void ls_finish_call(int nsteps) = 0;
+    virtual int device() const = 0;
 };
 
 template <typename R>
@@ -125,6 +151,10 @@ class SolverT final : public SolverBase {
         CK(cudaMalloc(&d_bst_, sizeof(BicgState<R>)));
         CK(cudaMemset(d_bst_, 0, sizeof(BicgState<R>)));
         d_scan_total_.alloc(1);
+        d_rhs_tot_.alloc(8);
+        CK(cudaMalloc(&d_loc_, sizeof(CommLocal)));
+        CK(cudaMemset(d_loc_, 0, sizeof(CommLocal)));
+        cm_.loc = d_loc_;
         if (const char* v = getenv("FEAB_SPMV")) spmv_variant_ = atoi(v);
         if (const char* v = getenv("FEAB_PREFETCH_X")) prefetch_x_ = atoi(v);
         setup_spmv_variants();
@@ -148,15 +178,18 @@ class SolverT final : public SolverBase {
         using Cfg = TmaCfg<R, ROWS, CPR, STAGES>;
         const int tiles = std::max(1, cdiv64(n_, ROWS));
         const int grid = std::min(tiles, sms_ * MINB);
-        spmv_dot_tma<R, ROWS, CPR, STAGES, MINB><<<grid, ROWS, Cfg::kSmemBytes, s>>>(d_rowptr_.p, d_col_.p, A, x, y, n_, tiles, st, part_pap(), prefetch_x_);
+        spmv_dot_tma<R, ROWS, CPR, STAGES, MINB><<<grid, ROWS, Cfg::kSmemBytes, s>>>(d_rowptr_.p, d_col_.p, A, x, y, n_, tiles, st, part_pap(), prefetch_x_,
+                                                                                     cm_, hp_, first_halo_tile(ROWS));
     }
     template <int ROWS, int MINB>
     int grid_tma() const {
         return std::min(std::max(1, cdiv64(n_, ROWS)), sms_ * MINB);
     }
     // number of p.Ap partials the SpMV of the current variant writes
+    // the LDG variant has no halo wait: a partitioned handle always runs a TMA pipeline
+    int spmv_variant() const { return (world_ > 1 && spmv_variant_ == 0) ? 4 : spmv_variant_; }
     int spmv_parts() const {
-        switch (spmv_variant_) {
+        switch (spmv_variant()) {
             case 1: return grid_tma<256, 2>();
             case 2: return grid_tma<512, 1>();
             case 3: return grid_tma<256, 3>();
@@ -166,7 +199,7 @@ class SolverT final : public SolverBase {
         }
     }
     void launch_spmv(cudaStream_t s, const R* A, const R* x, R* y, CgState<R>* st) {
-        switch (spmv_variant_) {
+        switch (spmv_variant()) {
             case 1: launch_tma<256, 10, 3, 2>(s, A, x, y, st); break;
             case 2: launch_tma<512, 9, 3, 1>(s, A, x, y, st); break;
             case 3: launch_tma<256, 10, 2, 3>(s, A, x, y, st); break;
@@ -184,6 +217,8 @@ class SolverT final : public SolverBase {
         if (d_unstable_) cudaFree(d_unstable_);
         if (d_st_) cudaFree(d_st_);
         if (d_bst_) cudaFree(d_bst_);
+        if (d_loc_) cudaFree(d_loc_);
+        close_peers();
         if (h_flag_) cudaFreeHost(h_flag_);
         cudaEventDestroy(ev0_);
         cudaEventDestroy(ev1_);
@@ -196,6 +231,16 @@ class SolverT final : public SolverBase {
         CK(cudaSetDevice(device_));
         REQUIRE(V > 0 && T >= 0 && xyz && onb && (T == 0 || tri), FEAB_EINVAL, "set_mesh: bad arguments");
         REQUIRE(V < (int64_t)INT32_MAX && 9 * T < (int64_t)INT32_MAX, FEAB_EINVAL, "set_mesh: mesh too large for int32 indexing");
+        // validate triangle indices on the host copy (the reference would index out of bounds)
+        for (int64_t i = 0; i < 3 * T; i++) REQUIRE(tri[i] < (uint64_t)V, FEAB_EINVAL, "set_mesh: triangle index out of range");
+        if (world_ > 1) {
+            if (part_given_) {
+                REQUIRE((int64_t)h_part_.size() == V, FEAB_EINVAL, "set_mesh: partition array length != num_vertices");
+            } else {  // default partition: recursive coordinate bisection, identical on every rank
+                h_part_.assign((size_t)V, 0);
+                rcb_partition(V, xyz, world_, h_part_.data());
+            }
+        }
         V_ = V;
         T_ = T;
         d_xyz_.alloc(3 * V);
@@ -204,11 +249,11 @@ class SolverT final : public SolverBase {
         CK(cudaMemcpyAsync(d_xyz_.p, xyz, 3 * V * sizeof(float), cudaMemcpyHostToDevice, stream_));
         if (T) CK(cudaMemcpyAsync(d_tri_.p, tri, 3 * T * sizeof(uint32_t), cudaMemcpyHostToDevice, stream_));
         CK(cudaMemcpyAsync(d_onb_.p, onb, V, cudaMemcpyHostToDevice, stream_));
-        d_values_.alloc(V);
-        CK(cudaMemsetAsync(d_values_.p, 0, V * sizeof(float), stream_));
+        if (world_ > 1) {
+            d_part_of_.alloc(V);
+            CK(cudaMemcpyAsync(d_part_of_.p, h_part_.data(), V * sizeof(int), cudaMemcpyHostToDevice, stream_));
+        }
         CK(cudaStreamSynchronize(stream_));
-        // validate triangle indices on the host copy (the reference would index out of bounds)
-        for (int64_t i = 0; i < 3 * T; i++) REQUIRE(tri[i] < (uint64_t)V, FEAB_EINVAL, "set_mesh: triangle index out of range");
         have_mesh_ = true;
         symbolic();
         assemble(nullptr);
@@ -241,9 +286,106 @@ class SolverT final : public SolverBase {
         }
     }
 
+    // Local numbering of a partition (partition.cuh): rows, ghost columns, send lists.  Everything is derived from
+    // the shared part[] array, identically on every rank.
+    void number_partition() {
+        const int64_t V = V_, T = T_, ng = nglob_;
+        const int gV = cdiv64(V, kBlock), gT = std::max(1, cdiv64(T, kBlock)), gU = std::max(1, cdiv64(ng, kBlock));
+        DevBuf<unsigned> mask;
+        DevBuf<int> flag, excl, lrow, lcol, cnt;
+        mask.alloc(std::max<int64_t>(ng, 1));
+        flag.alloc(ng + 1);
+        excl.alloc(ng + 2);
+        lrow.alloc(std::max<int64_t>(ng, 1));
+        lcol.alloc(std::max<int64_t>(ng, 1));
+        cnt.alloc(kMaxRanks * kMaxRanks);
+        CK(cudaMemsetAsync(mask.p, 0, std::max<int64_t>(ng, 1) * sizeof(unsigned), stream_));
+        CK(cudaMemsetAsync(lrow.p, 0xff, std::max<int64_t>(ng, 1) * sizeof(int), stream_));
+        CK(cudaMemsetAsync(cnt.p, 0, kMaxRanks * kMaxRanks * sizeof(int), stream_));
+        if (T) ghost_mask_build<<<gT, kBlock, 0, stream_>>>(d_tri_.p, T, d_idx_.p, d_part_of_.p, mask.p);
+        long long tot = 0;
+        // rows: interior first, boundary last
+        flag_unknowns<<<gU, kBlock, 0, stream_>>>(d_node_of_.p, d_part_of_.p, mask.p, ng, rank_, 0, 0, flag.p);
+        exclusive_scan(flag.p, ng, excl.p, &tot);
+        n_int_ = tot;
+        assign_ids<<<gU, kBlock, 0, stream_>>>(flag.p, excl.p, ng, 0, lrow.p);
+        flag_unknowns<<<gU, kBlock, 0, stream_>>>(d_node_of_.p, d_part_of_.p, mask.p, ng, rank_, 1, 0, flag.p);
+        exclusive_scan(flag.p, ng, excl.p, &tot);
+        assign_ids<<<gU, kBlock, 0, stream_>>>(flag.p, excl.p, ng, (int)n_int_, lrow.p);
+        n_ = n_int_ + tot;
+        const int64_t line = 128 / (int64_t)sizeof(R);  // ghosts start on their own 128-byte line (comm.cuh)
+        ghost_base_ = (n_ + line - 1) / line * line;
+        CK(cudaMemcpyAsync(lcol.p, lrow.p, std::max<int64_t>(ng, 1) * sizeof(int), cudaMemcpyDeviceToDevice, stream_));
+        // unknowns owned per rank (for the ghost base of every peer) and the ghost-pair counts
+        int64_t n_own_of[kMaxRanks] = {};
+        for (int q = 0; q < world_; q++) {
+            flag_unknowns<<<gU, kBlock, 0, stream_>>>(d_node_of_.p, d_part_of_.p, mask.p, ng, q, 3, 0, flag.p);
+            exclusive_scan(flag.p, ng, excl.p, &tot);
+            n_own_of[q] = tot;
+        }
+        count_ghost_pairs<<<std::min(gU, sms_ * 8), kBlock, 0, stream_>>>(d_node_of_.p, d_part_of_.p, mask.p, ng, cnt.p);
+        int h_cnt[kMaxRanks * kMaxRanks];
+        CK(cudaMemcpyAsync(h_cnt, cnt.p, sizeof(h_cnt), cudaMemcpyDeviceToHost, stream_));
+        CK(cudaStreamSynchronize(stream_));
+        // ghosts grouped by owner
+        int64_t goff = ghost_base_;
+        for (int q = 0; q < world_; q++) {
+            if (q == rank_ || h_cnt[q * kMaxRanks + rank_] == 0) continue;
+            flag_unknowns<<<gU, kBlock, 0, stream_>>>(d_node_of_.p, d_part_of_.p, mask.p, ng, q, 2, rank_, flag.p);
+            exclusive_scan(flag.p, ng, excl.p, &tot);
+            REQUIRE(tot == h_cnt[q * kMaxRanks + rank_], FEAB_EINVAL, "partition: ghost count mismatch");
+            assign_ids<<<gU, kBlock, 0, stream_>>>(flag.p, excl.p, ng, (int)goff, lcol.p);
+            goff += tot;
+        }
+        n_cols_ = goff;
+        n_ghost_ = goff - ghost_base_;
+        // send lists and where they land on each neighbour
+        hp_ = HaloPlan();
+        int64_t total_send = 0;
+        for (int q = 0; q < world_; q++)
+            if (q != rank_) total_send += h_cnt[rank_ * kMaxRanks + q];
+        d_send_rows_.alloc(std::max<int64_t>(total_send, 1));
+        d_send_nodes_.alloc(std::max<int64_t>(total_send, 1));
+        int64_t soff = 0;
+        for (int q = 0; q < world_; q++) {
+            const int c = h_cnt[rank_ * kMaxRanks + q];
+            if (q == rank_ || c == 0) continue;
+            flag_unknowns<<<gU, kBlock, 0, stream_>>>(d_node_of_.p, d_part_of_.p, mask.p, ng, rank_, 2, q, flag.p);
+            exclusive_scan(flag.p, ng, excl.p, &tot);
+            REQUIRE(tot == c, FEAB_EINVAL, "partition: send count mismatch");
+            gather_list<<<gU, kBlock, 0, stream_>>>(flag.p, excl.p, ng, lrow.p, d_node_of_.p, d_send_rows_.p + soff, d_send_nodes_.p + soff);
+            const int b = hp_.nnb++;
+            hp_.nb_rank[b] = q;
+            hp_.send_off[b] = (int)soff;
+            const int64_t gb_q = (n_own_of[q] + line - 1) / line * line;
+            int64_t before = 0;
+            for (int o = 0; o < rank_; o++)
+                if (o != q) before += h_cnt[o * kMaxRanks + q];
+            hp_.dst_col[b] = (int)(gb_q + before);
+            soff += c;
+            hp_.send_off[b + 1] = (int)soff;
+        }
+        hp_.send_rows = d_send_rows_.p;
+        hp_.send_nodes = d_send_nodes_.p;
+        // per-node maps and their inverses
+        d_rowmap_.alloc(V);
+        d_colmap_.alloc(V);
+        d_node_of_col_.alloc(std::max<int64_t>(n_cols_, 1));
+        d_glob_of_col_.alloc(std::max<int64_t>(n_cols_, 1));
+        CK(cudaMemsetAsync(d_node_of_col_.p, 0xff, std::max<int64_t>(n_cols_, 1) * sizeof(int), stream_));
+        CK(cudaMemsetAsync(d_glob_of_col_.p, 0xff, std::max<int64_t>(n_cols_, 1) * sizeof(int), stream_));
+        make_local_maps<<<gV, kBlock, 0, stream_>>>(d_idx_.p, lrow.p, lcol.p, V, d_rowmap_.p, d_colmap_.p, d_node_of_col_.p, d_glob_of_col_.p);
+        CK(cudaGetLastError());
+        CK(cudaStreamSynchronize(stream_));
+        rowmap_p_ = d_rowmap_.p;
+        colmap_p_ = d_colmap_.p;
+        node_of_col_p_ = d_node_of_col_.p;
+    }
+
     void symbolic() {
         drop_graphs();
         op_valid_ = false;
+        close_peers();
         const int64_t V = V_, T = T_;
         const int gV = cdiv64(V, kBlock), gT = std::max(1, cdiv64(T, kBlock));
         // --- idx_map (exclusive scan of the unknown flags) ---
@@ -253,11 +395,20 @@ class SolverT final : public SolverBase {
         unknown_flags<<<gV, kBlock, 0, stream_>>>(d_onb_.p, V, bc_, flag.p);
         long long n_ll = 0;
         exclusive_scan(flag.p, V, excl.p, &n_ll);
-        n_ = n_ll;
+        nglob_ = n_ll;
         d_idx_.alloc(V);
-        d_node_of_.alloc(std::max<int64_t>(n_, 1));
+        d_node_of_.alloc(std::max<int64_t>(nglob_, 1));
         make_idx_map<<<gV, kBlock, 0, stream_>>>(flag.p, excl.p, V, d_idx_.p, d_node_of_.p);
         launches_ += 2;
+        if (world_ > 1) {
+            number_partition();
+        } else {
+            n_ = n_int_ = ghost_base_ = n_cols_ = nglob_;
+            n_ghost_ = 0;
+            rowmap_p_ = colmap_p_ = d_idx_.p;
+            node_of_col_p_ = d_node_of_.p;
+            hp_ = HaloPlan();
+        }
         const int64_t n = n_;
         const int gN = std::max(1, cdiv64(n, kBlock));
         // --- row candidates -> sorted unique rows -> rowptr / col ---
@@ -268,12 +419,12 @@ class SolverT final : public SolverBase {
         rowlen.alloc(n + 1);
         CK(cudaMemsetAsync(cnt.p, 0, (n + 1) * sizeof(int), stream_));
         CK(cudaMemsetAsync(fill.p, 0, (n + 1) * sizeof(int), stream_));
-        if (T) count_row_candidates<<<gT, kBlock, 0, stream_>>>(d_tri_.p, T, d_idx_.p, cnt.p);
+        if (T) count_row_candidates<<<gT, kBlock, 0, stream_>>>(d_tri_.p, T, rowmap_p_, colmap_p_, cnt.p);
         long long ncand = 0;
         exclusive_scan(cnt.p, n, cptr.p, &ncand);
         REQUIRE(ncand < (long long)INT32_MAX, FEAB_EINVAL, "symbolic: candidate list exceeds int32");
         cand.alloc(std::max<long long>(ncand, 1));
-        if (T) fill_row_candidates<<<gT, kBlock, 0, stream_>>>(d_tri_.p, T, d_idx_.p, cptr.p, fill.p, cand.p);
+        if (T) fill_row_candidates<<<gT, kBlock, 0, stream_>>>(d_tri_.p, T, rowmap_p_, colmap_p_, cptr.p, fill.p, cand.p);
         sort_unique_rows<<<gN, kBlock, 0, stream_>>>(cptr.p, cand.p, n, rowlen.p);
         d_rowptr_.alloc(n + 1);
         long long nnz_ll = 0;
@@ -285,23 +436,22 @@ class SolverT final : public SolverBase {
         maxlen.alloc(1);
         CK(cudaMemsetAsync(maxlen.p, 0, sizeof(int), stream_));
         compact_rows<<<gN, kBlock, 0, stream_>>>(cptr.p, cand.p, d_rowptr_.p, n, d_col_.p, d_diag_.p, maxlen.p);
-        d_tpos_.alloc(std::max<int64_t>(nnz_, 1));
         d_advp_.alloc(std::max<int64_t>(nnz_, 1));
-        build_transpose_map<<<gN, kBlock, 0, stream_>>>(d_rowptr_.p, d_col_.p, n, d_node_of_.p, d_onb_.p, d_tpos_.p, d_advp_.p);
+        mark_adv_present<<<gN, kBlock, 0, stream_>>>(d_rowptr_.p, d_col_.p, n, node_of_col_p_, d_onb_.p, d_advp_.p);
         launches_ += 5;
         CK(cudaMemcpyAsync(&max_row_, maxlen.p, sizeof(int), cudaMemcpyDeviceToHost, stream_));
         // --- scatter map (scatter assembly) ---
         d_smap_.alloc(std::max<int64_t>(9 * T, 1));
-        if (T) build_scatter_map<<<gT, kBlock, 0, stream_>>>(d_tri_.p, T, d_idx_.p, d_rowptr_.p, d_col_.p, d_smap_.p);
+        if (T) build_scatter_map<<<gT, kBlock, 0, stream_>>>(d_tri_.p, T, rowmap_p_, colmap_p_, d_rowptr_.p, d_col_.p, d_smap_.p);
         // --- ordered corner adjacency (ordered assembly) ---
         d_cptr_.alloc(n + 1);
         CK(cudaMemsetAsync(cnt.p, 0, (n + 1) * sizeof(int), stream_));
         CK(cudaMemsetAsync(fill.p, 0, (n + 1) * sizeof(int), stream_));
-        if (T) count_row_corners<<<gT, kBlock, 0, stream_>>>(d_tri_.p, T, d_idx_.p, cnt.p);
+        if (T) count_row_corners<<<gT, kBlock, 0, stream_>>>(d_tri_.p, T, rowmap_p_, cnt.p);
         long long ncorner = 0;
         exclusive_scan(cnt.p, n, d_cptr_.p, &ncorner);
         d_corner_.alloc(std::max<long long>(ncorner, 1));
-        if (T) fill_row_corners<<<gT, kBlock, 0, stream_>>>(d_tri_.p, T, d_idx_.p, d_cptr_.p, fill.p, d_corner_.p);
+        if (T) fill_row_corners<<<gT, kBlock, 0, stream_>>>(d_tri_.p, T, rowmap_p_, d_cptr_.p, fill.p, d_corner_.p);
         sort_row_corners<<<gN, kBlock, 0, stream_>>>(d_cptr_.p, d_corner_.p, n);
         launches_ += 4;
         CK(cudaGetLastError());
@@ -311,34 +461,68 @@ class SolverT final : public SolverBase {
         d_M_.alloc(nz);
         d_K_.alloc(nz);
         d_Adv_.alloc(nz);
+        d_AdvT_.alloc(nz);
         d_Md_.alloc(nz);
         d_A0_.alloc(nz);
         d_A1_.alloc(nz);
         d_dinv0_.alloc(nn);
         d_dinv1_.alloc(nn);
         d_y_.alloc(nn);
-        for (int s = 0; s < 2; s++) {
-            d_r_[s].alloc(nn);
-            d_p_[s].alloc(nn);
-        }
+        for (int s = 0; s < 2; s++) d_r_[s].alloc(nn);
         for (int s = 0; s < 5; s++) d_w_[s].alloc(nn);
         num_tiles_ = std::max(1, cdiv64(n, kTileRows));
         g_tile_ = std::min(num_tiles_, sms_ * 8);
         g_vec_ = std::max(1, std::min(cdiv64(std::max<int64_t>(n / Vec<R>::N, 1), kBlock), sms_ * 8));
         g_part_ = std::max(std::max(g_tile_, g_vec_), sms_ * 8);
         d_part_.alloc((size_t)16 * g_part_);
-        resize_state();
+        alloc_arena();
+    }
+
+    // The vectors peers write into (ghost tails of p, u, v; the surface values) live in ONE allocation that starts
+    // with the CommCtrl mailboxes, so a peer needs a single mapping (feab_mg_export / feab_mg_connect).
+    void alloc_arena() {
+        const size_t nc = (size_t)std::max<int64_t>(n_cols_, 1) + kTmaPad;
+        auto pad = [](size_t b) { return (b + 255) / 256 * 256; };
+        size_t off = kCtrlBytes;
+        for (int v = 0; v < 4; v++) {
+            off_vec_[v] = off;
+            off += pad(nc * sizeof(R));
+        }
+        off_vec_[kVecValues] = off;
+        off += pad(((size_t)V_ + kTmaPad) * sizeof(float));
+        d_arena_.release();
+        d_arena_.alloc(off);
+        CK(cudaMemsetAsync(d_arena_.p, 0, off, stream_));
+        unsigned char* base = d_arena_.p;
+        d_p_[0].view(base + off_vec_[kVecP0], nc);
+        d_p_[1].view(base + off_vec_[kVecP1], nc);
+        d_u_.view(base + off_vec_[kVecU], nc);
+        d_v_.view(base + off_vec_[kVecV], nc);
+        d_values_.view(base + off_vec_[kVecValues], (size_t)V_);
+        CK(cudaMemsetAsync(d_loc_, 0, sizeof(CommLocal), stream_));
+        CK(cudaStreamSynchronize(stream_));
+        cm_ = Comm();
+        cm_.rank = rank_;
+        cm_.world = world_;
+        cm_.loc = d_loc_;
+        cm_.ctrl[rank_] = reinterpret_cast<CommCtrl*>(base);
+        hp_.base[rank_] = reinterpret_cast<char*>(base);
+        for (int v = 0; v < 5; v++) hp_.off_vec[v][rank_] = off_vec_[v];
+        for (int q = 0; q < kMaxRanks; q++) connected_[q] = (q == rank_);
+    }
+
+    void close_peers() {
+        for (int q = 0; q < kMaxRanks; q++) {
+            if (ipc_opened_[q]) cudaIpcCloseMemHandle(ipc_opened_[q]);
+            ipc_opened_[q] = nullptr;
+            connected_[q] = false;
+        }
     }
 
     void resize_state() {
-        const int64_t nn = std::max<int64_t>(n_, 1);
-        if (d_u_.count != (size_t)nn || !d_u_.p) {
-            d_u_.alloc(nn);
-            d_v_.alloc(nn);
-            drop_graphs();
-        }
-        CK(cudaMemsetAsync(d_u_.p, 0, nn * sizeof(R), stream_));
-        CK(cudaMemsetAsync(d_v_.p, 0, nn * sizeof(R), stream_));
+        const int64_t nc = std::max<int64_t>(n_cols_, 1);
+        CK(cudaMemsetAsync(d_u_.p, 0, nc * sizeof(R), stream_));
+        CK(cudaMemsetAsync(d_v_.p, 0, nc * sizeof(R), stream_));
         CK(cudaStreamSynchronize(stream_));
     }
 
@@ -350,18 +534,19 @@ class SolverT final : public SolverBase {
         const int64_t nz = std::max<int64_t>(nnz_, 1);
         if (opt_.assembly == FEAB_ASSEMBLY_ORDERED) {
             if (n_ > 0) {
-                assemble_ordered<R><<<cdiv64(n_, kBlock), kBlock, 0, stream_>>>(d_xyz_.p, d_tri_.p, n_, d_onb_.p, d_idx_.p, d_cptr_.p,
+                assemble_ordered<R><<<cdiv64(n_, kBlock), kBlock, 0, stream_>>>(d_xyz_.p, d_tri_.p, n_, d_onb_.p, colmap_p_, d_cptr_.p,
                                                                                   d_corner_.p, d_rowptr_.p, d_col_.p, (R)vel_[0], (R)vel_[1],
-                                                                                  (R)vel_[2], d_M_.p, d_K_.p, d_Adv_.p);
+                                                                                  (R)vel_[2], d_M_.p, d_K_.p, d_Adv_.p, d_AdvT_.p);
                 launches_++;
             }
         } else {
             CK(cudaMemsetAsync(d_M_.p, 0, nz * sizeof(R), stream_));
             CK(cudaMemsetAsync(d_K_.p, 0, nz * sizeof(R), stream_));
             CK(cudaMemsetAsync(d_Adv_.p, 0, nz * sizeof(R), stream_));
+            CK(cudaMemsetAsync(d_AdvT_.p, 0, nz * sizeof(R), stream_));
             if (T_ > 0) {
                 assemble_scatter<R><<<cdiv64(T_, kBlock), kBlock, 0, stream_>>>(d_xyz_.p, d_tri_.p, T_, d_onb_.p, d_smap_.p, (R)vel_[0],
-                                                                                  (R)vel_[1], (R)vel_[2], d_M_.p, d_K_.p, d_Adv_.p);
+                                                                                  (R)vel_[1], (R)vel_[2], d_M_.p, d_K_.p, d_Adv_.p, d_AdvT_.p);
                 launches_++;
             }
         }
@@ -500,19 +685,20 @@ class SolverT final : public SolverBase {
     }
     bool use_bicgstab() const { return eq_ == FEAB_EQ_ADVECTION_DIFFUSION && opt_.solver == FEAB_SOLVER_BICGSTAB; }
 
-    void ensure_operator() {
+    void ensure_operator() { ensure_operator_on(stream_); }
+    void ensure_operator_on(cudaStream_t s) {
         const FeabParams& p = par_[eq_];
         const int transposed = (eq_ == FEAB_EQ_ADVECTION_DIFFUSION && !use_bicgstab()) ? 1 : 0;
         if (op_valid_ && op_eq_ == eq_ && op_transposed_ == transposed && std::memcmp(&op_par_, &p, sizeof(p)) == 0) return;
         REQUIRE(p.time_step != 0.0f, FEAB_EINVAL, "time_step must be non-zero");
         if (nnz_ > 0) {
             int g = std::min(cdiv64(nnz_, kBlock), sms_ * 16);
-            build_operator<R><<<g, kBlock, 0, stream_>>>(eq_, transposed, nnz_, d_M_.p, d_K_.p, d_Adv_.p, d_tpos_.p, scalars(), d_Md_.p, d_A0_.p,
+            build_operator<R><<<g, kBlock, 0, s>>>(eq_, transposed, nnz_, d_M_.p, d_K_.p, d_Adv_.p, d_AdvT_.p, scalars(), d_Md_.p, d_A0_.p,
                                                          d_A1_.p);
-            inv_diag<R><<<cdiv64(n_, kBlock), kBlock, 0, stream_>>>(d_A0_.p, d_diag_.p, n_, d_dinv0_.p);
+            inv_diag<R><<<cdiv64(n_, kBlock), kBlock, 0, s>>>(d_A0_.p, d_diag_.p, n_, d_dinv0_.p);
             launches_ += 2;
             if (eq_ == FEAB_EQ_REACTION_DIFFUSION) {
-                inv_diag<R><<<cdiv64(n_, kBlock), kBlock, 0, stream_>>>(d_A1_.p, d_diag_.p, n_, d_dinv1_.p);
+                inv_diag<R><<<cdiv64(n_, kBlock), kBlock, 0, s>>>(d_A1_.p, d_diag_.p, n_, d_dinv1_.p);
                 launches_++;
             }
             CK(cudaGetLastError());
@@ -538,18 +724,101 @@ class SolverT final : public SolverBase {
     R* part_rhs() { return d_part_.p + (size_t)3 * g_part_; }   // 4 x g_tile_
     R* part_bi() { return d_part_.p + (size_t)8 * g_part_; }    // 8 x g_part_ for BiCGSTAB
 
-    void launch_iteration(cudaStream_t s, int slot, const R* A, const R* dinv, R* x, cudaGraphConditionalHandle cond, int use_cond) {
+    // ---- phases of one time step (the same code is captured into the step graph, launched directly in
+    //      host-batched mode, and driven in lock-step over several handles by feab_mg_group_step) ----
+    int first_halo_tile(int rows_per_tile) const { return world_ > 1 ? (int)(n_int_ / rows_per_tile) : INT32_MAX; }
+
+    void ph_push_state(cudaStream_t s) {  // ghosts of u, v and the surface values of boundary rows -> neighbours
+        if (world_ == 1) return;
+        state_push<R><<<1, 1024, 0, s>>>(cm_, hp_, d_u_.p, d_v_.p, d_values_.p);
+        launches_++;
+    }
+    void ph_step_begin(cudaStream_t s, bool capturing) {
+        const int gV = cdiv64(V_, kBlock);
+        const StepScalars sc = scalars();
+        const size_t sm2 = 2 * kTileCap * sizeof(R);
+        if (world_ > 1) wait_kernel<<<1, 32, 0, s>>>(cm_, hp_, 1);
+        CK(cudaMemsetAsync(d_unstable_, 0, sizeof(int), s));
+        R* target = eq_ == FEAB_EQ_REACTION_DIFFUSION ? d_v_.p : d_u_.p;
+        gather_values<R><<<gV, kBlock, 0, s>>>(d_values_.p, colmap_p_, V_, target);
+        R* prt = part_rhs();
+#define FEAB_RHS(EQ)                                                                                                            \
+    rhs_init<R, EQ><<<g_tile_, kBlock, sm2, s>>>(d_rowptr_.p, d_col_.p, d_Md_.p, d_K_.p, d_u_.p, d_v_.p, d_dinv0_.p, d_dinv1_.p, n_, \
+                                                 num_tiles_, sc, d_r_[0].p, d_p_[0].p, d_r_[1].p, d_p_[1].p, prt, cm_)
+        switch (eq_) {
+            case FEAB_EQ_HEAT: FEAB_RHS(0); break;
+            case FEAB_EQ_WAVE: FEAB_RHS(1); break;
+            case FEAB_EQ_ADVECTION_DIFFUSION: FEAB_RHS(2); break;
+            default: FEAB_RHS(3); break;
+        }
+#undef FEAB_RHS
+        if (!capturing) launches_ += 2;
+        CK(cudaGetLastError());
+    }
+    // partitioned: totals of the RHS dot products for cg_begin, first search directions to the neighbours.
+    // A separate phase: it consumes what EVERY rank's rhs_init published.
+    void ph_step_collect(cudaStream_t s, bool capturing) {
+        if (world_ > 1) {
+            const bool gs = eq_ == FEAB_EQ_REACTION_DIFFUSION;
+            if (gs)
+                ar_collect<R, 4><<<1, 32, 0, s>>>(cm_, d_rhs_tot_.p);
+            else
+                ar_collect<R, 2><<<1, 32, 0, s>>>(cm_, d_rhs_tot_.p);
+            halo_push<R><<<1, 1024, 0, s>>>(cm_, hp_, d_p_[0].p, kVecP0, gs ? d_p_[1].p : (const R*)nullptr, kVecP1);
+            if (!capturing) launches_ += 3;
+        }
+        CK(cudaGetLastError());
+    }
+    void ph_cg_begin(cudaStream_t s, int slot, R* x, cudaGraphConditionalHandle cond, int use_cond) {
         CgState<R>* st = d_st_ + slot;
-        launch_spmv(s, A, d_p_[slot].p, d_y_.p, st);
-        cg_update<R><<<g_vec_, kBlock, 0, s>>>(x, d_r_[slot].p, d_p_[slot].p, d_y_.p, dinv, n_, st, part_pap(), spmv_parts(), part_rr(), part_rz());
-        cg_direction<R><<<g_vec_, kBlock, 0, s>>>(d_r_[slot].p, d_p_[slot].p, dinv, n_, st, part_rr(), part_rz(), g_vec_, cond, use_cond);
+        CK(cudaMemsetAsync(x, 0, n_ * sizeof(R), s));
+        if (world_ > 1) {
+            const R* tot = d_rhs_tot_.p + 2 * slot;
+            cg_begin<R><<<1, kBlock, 0, s>>>(st, tot, tot + 1, 1, tol(), maxit(), cond, use_cond);
+        } else {
+            const R* rhs = part_rhs() + (size_t)(slot * 2) * g_tile_;
+            cg_begin<R><<<1, kBlock, 0, s>>>(st, rhs, rhs + g_tile_, g_tile_, tol(), maxit(), cond, use_cond);
+        }
+    }
+    void ph_spmv(cudaStream_t s, int slot, const R* A) { launch_spmv(s, A, d_p_[slot].p, d_y_.p, d_st_ + slot); }
+    void ph_update(cudaStream_t s, int slot, const R* dinv, R* x) {
+        cg_update<R><<<g_vec_, kBlock, 0, s>>>(x, d_r_[slot].p, d_p_[slot].p, d_y_.p, dinv, n_, d_st_ + slot, part_pap(), spmv_parts(), part_rr(),
+                                               part_rz(), cm_);
+    }
+    void ph_direction(cudaStream_t s, int slot, const R* dinv, cudaGraphConditionalHandle cond, int use_cond) {
+        cg_direction<R><<<g_vec_, kBlock, 0, s>>>(d_r_[slot].p, d_p_[slot].p, dinv, n_, d_st_ + slot, part_rr(), part_rz(), g_vec_, cond, use_cond,
+                                                  cm_);
+        if (world_ > 1) halo_push<R><<<1, 1024, 0, s>>>(cm_, hp_, d_p_[slot].p, slot == 0 ? kVecP0 : kVecP1, (const R*)nullptr, 0);
+    }
+    int kernels_per_iteration() const { return world_ > 1 ? 4 : 3; }
+    void ph_finish(cudaStream_t s, bool capturing) {
+        const int gV = cdiv64(V_, kBlock);
+        finish_step<R><<<gV, kBlock, 0, s>>>(d_values_.p, d_idx_.p, rowmap_p_, V_, d_u_.p, d_v_.p, eq_ == FEAB_EQ_WAVE ? 1 : 0, (R)scalars().dt,
+                                             eq_ == FEAB_EQ_REACTION_DIFFUSION ? 1 : 0, d_unstable_);
+        if (world_ > 1) state_push<R><<<1, 1024, 0, s>>>(cm_, hp_, d_u_.p, d_v_.p, d_values_.p);
+        if (!capturing) launches_ += world_ > 1 ? 2 : 1;
+        CK(cudaGetLastError());
+    }
+    // the solves of the current equation: (operator, inverse diagonal, solution vector)
+    int solves(const R* A[2], const R* dinv[2], R* x[2]) {
+        A[0] = d_A0_.p;
+        dinv[0] = d_dinv0_.p;
+        x[0] = eq_ == FEAB_EQ_WAVE ? d_v_.p : d_u_.p;
+        A[1] = d_A1_.p;
+        dinv[1] = d_dinv1_.p;
+        x[1] = d_v_.p;
+        return eq_ == FEAB_EQ_REACTION_DIFFUSION ? 2 : 1;
+    }
+
+    void launch_iteration(cudaStream_t s, int slot, const R* A, const R* dinv, R* x, cudaGraphConditionalHandle cond, int use_cond) {
+        ph_spmv(s, slot, A);
+        ph_update(s, slot, dinv, x);
+        ph_direction(s, slot, dinv, cond, use_cond);
     }
 
     // PCG solve of slot `slot` into x.  capturing: build WHILE node into the graph being captured on stream_.
     void enqueue_pcg(int slot, const R* A, const R* dinv, R* x, bool capturing) {
         CgState<R>* st = d_st_ + slot;
-        const R* rhs = part_rhs() + (size_t)(slot * 2) * g_tile_;
-        CK(cudaMemsetAsync(x, 0, n_ * sizeof(R), stream_));
         if (capturing) {
             cudaStreamCaptureStatus status;
             cudaGraph_t graph;
@@ -558,7 +827,7 @@ class SolverT final : public SolverBase {
             CK(cudaStreamGetCaptureInfo(stream_, &status, nullptr, &graph, &deps, &ndeps));
             cudaGraphConditionalHandle cond;
             CK(cudaGraphConditionalHandleCreate(&cond, graph, 0, 0));
-            cg_begin<R><<<1, kBlock, 0, stream_>>>(st, rhs, rhs + g_tile_, g_tile_, tol(), maxit(), cond, 1);
+            ph_cg_begin(stream_, slot, x, cond, 1);
             CK(cudaStreamGetCaptureInfo(stream_, &status, nullptr, &graph, &deps, &ndeps));
             cudaGraphNodeParams np = {cudaGraphNodeTypeConditional};
             np.type = cudaGraphNodeTypeConditional;
@@ -574,13 +843,13 @@ class SolverT final : public SolverBase {
             CK(cudaStreamEndCapture(stream2_, nullptr));
         } else {
             cudaGraphConditionalHandle none = 0;
-            cg_begin<R><<<1, kBlock, 0, stream_>>>(st, rhs, rhs + g_tile_, g_tile_, tol(), maxit(), none, 0);
+            ph_cg_begin(stream_, slot, x, none, 0);
             launches_ += 1;
             const int batch = 8;
             const int64_t mi = maxit();
             for (int64_t done_iters = 0; done_iters < mi + batch;) {
                 for (int b = 0; b < batch; b++) launch_iteration(stream_, slot, A, dinv, x, none, 0);
-                launches_ += 3 * batch;
+                launches_ += kernels_per_iteration() * batch;
                 done_iters += batch;
                 CK(cudaMemcpyAsync(h_flag_, &st->done, sizeof(int), cudaMemcpyDeviceToHost, stream_));
                 CK(cudaStreamSynchronize(stream_));
@@ -593,51 +862,18 @@ class SolverT final : public SolverBase {
     void enqueue_bicgstab(const R* A, const R* dinv, R* x, bool capturing);  // bicgstab driver below
 
     void enqueue_step(bool capturing) {
-        const int gV = cdiv64(V_, kBlock);
-        const StepScalars sc = scalars();
-        const size_t sm2 = 2 * kTileCap * sizeof(R);
-        CK(cudaMemsetAsync(d_unstable_, 0, sizeof(int), stream_));
-        R* target = eq_ == FEAB_EQ_REACTION_DIFFUSION ? d_v_.p : d_u_.p;
-        gather_values<R><<<gV, kBlock, 0, stream_>>>(d_values_.p, d_idx_.p, V_, target);
-        R* prt = part_rhs();
-        switch (eq_) {
-            case FEAB_EQ_HEAT:
-                rhs_init<R, 0><<<g_tile_, kBlock, sm2, stream_>>>(d_rowptr_.p, d_col_.p, d_Md_.p, d_K_.p, d_u_.p, d_v_.p, d_dinv0_.p, d_dinv1_.p, n_,
-                                                                  num_tiles_, sc, d_r_[0].p, d_p_[0].p, d_r_[1].p, d_p_[1].p, prt);
-                break;
-            case FEAB_EQ_WAVE:
-                rhs_init<R, 1><<<g_tile_, kBlock, sm2, stream_>>>(d_rowptr_.p, d_col_.p, d_Md_.p, d_K_.p, d_u_.p, d_v_.p, d_dinv0_.p, d_dinv1_.p, n_,
-                                                                  num_tiles_, sc, d_r_[0].p, d_p_[0].p, d_r_[1].p, d_p_[1].p, prt);
-                break;
-            case FEAB_EQ_ADVECTION_DIFFUSION:
-                rhs_init<R, 2><<<g_tile_, kBlock, sm2, stream_>>>(d_rowptr_.p, d_col_.p, d_Md_.p, d_K_.p, d_u_.p, d_v_.p, d_dinv0_.p, d_dinv1_.p, n_,
-                                                                  num_tiles_, sc, d_r_[0].p, d_p_[0].p, d_r_[1].p, d_p_[1].p, prt);
-                break;
-            default:
-                rhs_init<R, 3><<<g_tile_, kBlock, sm2, stream_>>>(d_rowptr_.p, d_col_.p, d_Md_.p, d_K_.p, d_u_.p, d_v_.p, d_dinv0_.p, d_dinv1_.p, n_,
-                                                                  num_tiles_, sc, d_r_[0].p, d_p_[0].p, d_r_[1].p, d_p_[1].p, prt);
-                break;
+        ph_step_begin(stream_, capturing);
+        ph_step_collect(stream_, capturing);
+        if (use_bicgstab()) {
+            enqueue_bicgstab(d_A0_.p, d_dinv0_.p, d_u_.p, capturing);
+        } else {
+            const R* A[2];
+            const R* dinv[2];
+            R* x[2];
+            const int ns = solves(A, dinv, x);
+            for (int slot = 0; slot < ns; slot++) enqueue_pcg(slot, A[slot], dinv[slot], x[slot], capturing);
         }
-        if (!capturing) launches_ += 2;
-        CK(cudaGetLastError());
-        switch (eq_) {
-            case FEAB_EQ_HEAT: enqueue_pcg(0, d_A0_.p, d_dinv0_.p, d_u_.p, capturing); break;
-            case FEAB_EQ_WAVE: enqueue_pcg(0, d_A0_.p, d_dinv0_.p, d_v_.p, capturing); break;
-            case FEAB_EQ_ADVECTION_DIFFUSION:
-                if (use_bicgstab())
-                    enqueue_bicgstab(d_A0_.p, d_dinv0_.p, d_u_.p, capturing);
-                else
-                    enqueue_pcg(0, d_A0_.p, d_dinv0_.p, d_u_.p, capturing);
-                break;
-            default:
-                enqueue_pcg(0, d_A0_.p, d_dinv0_.p, d_u_.p, capturing);
-                enqueue_pcg(1, d_A1_.p, d_dinv1_.p, d_v_.p, capturing);
-                break;
-        }
-        finish_step<R><<<gV, kBlock, 0, stream_>>>(d_values_.p, d_idx_.p, V_, d_u_.p, d_v_.p, eq_ == FEAB_EQ_WAVE ? 1 : 0, (R)sc.dt,
-                                                   eq_ == FEAB_EQ_REACTION_DIFFUSION ? 1 : 0, d_unstable_);
-        if (!capturing) launches_ += 1;
-        CK(cudaGetLastError());
+        ph_finish(stream_, capturing);
     }
 
     void drop_graphs() {
@@ -664,14 +900,42 @@ class SolverT final : public SolverBase {
         graph_eq_ = eq_;
     }
 
-    void step(float* values, int nsteps, int sync) override {
+    void require_ready_for_step() {
         REQUIRE(have_mesh_, FEAB_ENOMESH, "step: no mesh");
+        if (world_ > 1) {
+            for (int q = 0; q < world_; q++) REQUIRE(connected_[q], FEAB_EINVAL, "step: partitioned handle is not connected to every peer (feab_mg_connect)");
+            REQUIRE(!use_bicgstab(), FEAB_EINVAL, "step: BiCGSTAB is not available on a partitioned mesh (use FEAB_SOLVER_PARITY_CG)");
+            REQUIRE(n_ > 0, FEAB_EINVAL, "step: this rank owns no unknowns");
+        }
+    }
+    void check_comm_error() {
+        if (world_ == 1) return;
+        CommLocal l;
+        CK(cudaMemcpy(&l, d_loc_, sizeof(l), cudaMemcpyDeviceToHost));
+        if (l.error) {
+            CK(cudaMemset(&d_loc_->error, 0, sizeof(int)));
+            throw Err{FEAB_ECOMM, "step: timed out waiting for a peer (halo flag or all-reduce slot never arrived)"};
+        }
+    }
+    // surface->values complete on every rank: owners broadcast, everybody waits for everybody
+    void ph_broadcast_values(cudaStream_t s) {
+        if (world_ == 1) return;
+        const int g = std::max(1, std::min(cdiv64(n_, kBlock), sms_ * 4));
+        values_broadcast<<<g, kBlock, 0, s>>>(cm_, hp_, node_of_col_p_, n_, d_values_.p);
+        wait_kernel<<<1, 32, 0, s>>>(cm_, hp_, 2);
+        launches_ += 2;
+    }
+
+    void step(float* values, int nsteps, int sync) override {
+        require_ready_for_step();
         REQUIRE(nsteps >= 0, FEAB_EINVAL, "step: nsteps < 0");
+        REQUIRE(!lockstep_, FEAB_EINVAL, "step: this handle belongs to a lock-step group (use feab_mg_group_step)");
         CK(cudaSetDevice(device_));
         CK(cudaEventRecord(ev0_, stream_));
         if (values) CK(cudaMemcpyAsync(d_values_.p, values, V_ * sizeof(float), cudaMemcpyHostToDevice, stream_));
         if (n_ > 0 && nsteps > 0) {
             ensure_operator();
+            ph_push_state(stream_);
             const bool graph_mode = opt_.loop_mode == FEAB_LOOP_GRAPH_WHILE;
             if (graph_mode && (!graph_exec_ || graph_eq_ != eq_)) build_graph();
             for (int s = 0; s < nsteps; s++) {
@@ -683,7 +947,10 @@ class SolverT final : public SolverBase {
                 }
             }
         }
-        if (values && sync) CK(cudaMemcpyAsync(values, d_values_.p, V_ * sizeof(float), cudaMemcpyDeviceToHost, stream_));
+        if (values && sync) {
+            ph_broadcast_values(stream_);
+            CK(cudaMemcpyAsync(values, d_values_.p, V_ * sizeof(float), cudaMemcpyDeviceToHost, stream_));
+        }
         CK(cudaEventRecord(ev1_, stream_));
         CK(cudaStreamSynchronize(stream_));
         float ms = 0;
@@ -691,6 +958,7 @@ class SolverT final : public SolverBase {
         last_ms_ = ms;
         last_steps_ = nsteps;
         if (n_ > 0 && nsteps > 0 && opt_.loop_mode == FEAB_LOOP_GRAPH_WHILE) account_graph_launches(nsteps);
+        check_comm_error();
     }
 
     void read_states(CgState<R>* st2, BicgState<R>* bst) {
@@ -703,12 +971,12 @@ class SolverT final : public SolverBase {
         CgState<R> st[2];
         BicgState<R> b;
         read_states(st, &b);
-        int64_t per_step = 3;  // gather, rhs, finish
+        int64_t per_step = world_ > 1 ? 7 : 3;  // gather, rhs, finish (+ wait, collect, halo push, state push)
         if (use_bicgstab()) {
             per_step += 1 + (int64_t)kBicgKernelsPerIter * b.trips;
         } else {
-            per_step += 1 + 3 * (int64_t)st[0].iter1;
-            if (eq_ == FEAB_EQ_REACTION_DIFFUSION) per_step += 1 + 3 * (int64_t)st[1].iter1;
+            per_step += 1 + kernels_per_iteration() * (int64_t)st[0].iter1;
+            if (eq_ == FEAB_EQ_REACTION_DIFFUSION) per_step += 1 + kernels_per_iteration() * (int64_t)st[1].iter1;
         }
         launches_ += per_step * nsteps;
     }
@@ -741,6 +1009,8 @@ class SolverT final : public SolverBase {
     void time_kernel(int kernel, int reps, double* ms_out, double* bytes_out) override {
         REQUIRE(have_mesh_ && n_ > 0, FEAB_ENOMESH, "time_kernel: no mesh");
         REQUIRE(reps > 0 && kernel >= 0 && kernel <= 3, FEAB_EINVAL, "time_kernel: bad arguments");
+        REQUIRE(world_ == 1, FEAB_EINVAL, "time_kernel: single-GPU handles only (partitioned kernels wait for their peers)");
+        const Comm one;
         CK(cudaSetDevice(device_));
         ensure_operator();
         const double n = (double)n_, nnz = (double)nnz_, rb = sizeof(R);
@@ -768,24 +1038,24 @@ class SolverT final : public SolverBase {
                     break;
                 case 1:
                     cg_update<R><<<g_vec_, kBlock, 0, stream_>>>(d_w_[0].p, d_r_[0].p, d_p_[0].p, d_y_.p, d_dinv0_.p, n_, d_st_, part_pap(), spmv_parts(),
-                                                                 part_rr(), part_rz());
+                                                                 part_rr(), part_rz(), one);
                     break;
                 case 2:
-                    cg_direction<R><<<g_vec_, kBlock, 0, stream_>>>(d_r_[0].p, d_p_[0].p, d_dinv0_.p, n_, d_st_, part_rr(), part_rz(), g_vec_, none, 0);
+                    cg_direction<R><<<g_vec_, kBlock, 0, stream_>>>(d_r_[0].p, d_p_[0].p, d_dinv0_.p, n_, d_st_, part_rr(), part_rz(), g_vec_, none, 0, one);
                     break;
                 default:
                     if (eq_ == FEAB_EQ_REACTION_DIFFUSION)
                         rhs_init<R, 3><<<g_tile_, kBlock, 2 * kTileCap * sizeof(R), stream_>>>(d_rowptr_.p, d_col_.p, d_Md_.p, d_K_.p, d_u_.p, d_v_.p,
                                                                                                d_dinv0_.p, d_dinv1_.p, n_, num_tiles_, sc, d_r_[0].p,
-                                                                                               d_p_[0].p, d_r_[1].p, d_p_[1].p, part_rhs());
+                                                                                               d_p_[0].p, d_r_[1].p, d_p_[1].p, part_rhs(), one);
                     else if (eq_ == FEAB_EQ_WAVE)
                         rhs_init<R, 1><<<g_tile_, kBlock, 2 * kTileCap * sizeof(R), stream_>>>(d_rowptr_.p, d_col_.p, d_Md_.p, d_K_.p, d_u_.p, d_v_.p,
                                                                                                d_dinv0_.p, d_dinv1_.p, n_, num_tiles_, sc, d_r_[0].p,
-                                                                                               d_p_[0].p, d_r_[1].p, d_p_[1].p, part_rhs());
+                                                                                               d_p_[0].p, d_r_[1].p, d_p_[1].p, part_rhs(), one);
                     else
                         rhs_init<R, 0><<<g_tile_, kBlock, 2 * kTileCap * sizeof(R), stream_>>>(d_rowptr_.p, d_col_.p, d_Md_.p, d_K_.p, d_u_.p, d_v_.p,
                                                                                                d_dinv0_.p, d_dinv1_.p, n_, num_tiles_, sc, d_r_[0].p,
-                                                                                               d_p_[0].p, d_r_[1].p, d_p_[1].p, part_rhs());
+                                                                                               d_p_[0].p, d_r_[1].p, d_p_[1].p, part_rhs(), one);
                     break;
             }
         };
@@ -820,6 +1090,143 @@ class SolverT final : public SolverBase {
         CK(cudaMemset(d_st_, 0, 2 * sizeof(CgState<R>)));
     }
 
+    // ---------------------------------------------------------------- partitioned solve: configuration
+    void mg_config(int rank, int world) override {
+        REQUIRE(world >= 1 && world <= kMaxRanks && rank >= 0 && rank < world, FEAB_EINVAL, "mg_config: need 0 <= rank < world <= 8");
+        REQUIRE(!have_mesh_, FEAB_EINVAL, "mg_config: must be called before feab_set_mesh");
+        rank_ = rank;
+        world_ = world;
+    }
+    void mg_set_partition(const int32_t* part, int64_t V) override {
+        REQUIRE(part && V > 0, FEAB_EINVAL, "mg_set_partition: bad arguments");
+        REQUIRE(!have_mesh_, FEAB_EINVAL, "mg_set_partition: must be called before feab_set_mesh");
+        for (int64_t i = 0; i < V; i++) REQUIRE(part[i] >= 0 && part[i] < world_, FEAB_EINVAL, "mg_set_partition: part id out of range");
+        h_part_.assign(part, part + V);
+        part_given_ = true;
+    }
+    void mg_export(FeabMgExport* e) override {
+        REQUIRE(have_mesh_ && e, FEAB_ENOMESH, "mg_export: no mesh");
+        CK(cudaSetDevice(device_));
+        std::memset(e, 0, sizeof(*e));
+        cudaIpcMemHandle_t hd;
+        if (cudaIpcGetMemHandle(&hd, d_arena_.p) == cudaSuccess)
+            std::memcpy(e->ipc_handle, &hd, sizeof(hd));
+        else
+            cudaGetLastError();  // same-process connections do not need it
+        e->base_ptr = (uint64_t)(uintptr_t)d_arena_.p;
+        e->arena_bytes = d_arena_.count;
+        for (int v = 0; v < 5; v++) e->off_vec[v] = off_vec_[v];
+        e->n_own = n_;
+        e->n_ghost = n_ghost_;
+        e->ghost_base = ghost_base_;
+        e->num_nodes = V_;
+        e->rank = rank_;
+        e->world = world_;
+        e->device = device_;
+        e->pid = (int32_t)getpid();
+    }
+    void mg_connect(int q, const FeabMgExport* e, int same_process) override {
+        REQUIRE(have_mesh_ && e, FEAB_ENOMESH, "mg_connect: no mesh");
+        REQUIRE(world_ > 1 && q >= 0 && q < world_ && q != rank_, FEAB_EINVAL, "mg_connect: bad peer rank");
+        REQUIRE(e->rank == q && e->world == world_ && e->num_nodes == V_, FEAB_EINVAL, "mg_connect: export does not belong to that peer / mesh");
+        CK(cudaSetDevice(device_));
+        char* base = nullptr;
+        if (same_process) {
+            base = reinterpret_cast<char*>((uintptr_t)e->base_ptr);
+            if (e->device != device_) {
+                cudaError_t pe = cudaDeviceEnablePeerAccess(e->device, 0);
+                if (pe != cudaSuccess && pe != cudaErrorPeerAccessAlreadyEnabled) CK(pe);
+                cudaGetLastError();
+            }
+        } else {
+            if (ipc_opened_[q]) {
+                cudaIpcCloseMemHandle(ipc_opened_[q]);
+                ipc_opened_[q] = nullptr;
+            }
+            cudaIpcMemHandle_t hd;
+            std::memcpy(&hd, e->ipc_handle, sizeof(hd));
+            void* ptr = nullptr;
+            CK(cudaIpcOpenMemHandle(&ptr, hd, cudaIpcMemLazyEnablePeerAccess));
+            ipc_opened_[q] = ptr;
+            base = static_cast<char*>(ptr);
+        }
+        for (int b = 0; b < hp_.nnb; b++)
+            if (hp_.nb_rank[b] == q) {
+                const int64_t cnt = hp_.send_off[b + 1] - hp_.send_off[b];
+                REQUIRE(hp_.dst_col[b] >= e->ghost_base && hp_.dst_col[b] + cnt <= e->ghost_base + e->n_ghost, FEAB_EINVAL,
+                        "mg_connect: peer's ghost layout disagrees with this rank's send list (different mesh or partition?)");
+            }
+        cm_.ctrl[q] = reinterpret_cast<CommCtrl*>(base);
+        hp_.base[q] = base;
+        for (int v = 0; v < 5; v++) hp_.off_vec[v][q] = e->off_vec[v];
+        connected_[q] = true;
+        drop_graphs();  // the step graph bakes Comm / HaloPlan into its kernel nodes
+    }
+    void mg_get_layout(int64_t* n_own, int64_t* n_int, int64_t* n_ghost, int64_t* n_cols) override {
+        REQUIRE(have_mesh_, FEAB_ENOMESH, "mg_get_layout: no mesh");
+        if (n_own) *n_own = n_;
+        if (n_int) *n_int = n_int_;
+        if (n_ghost) *n_ghost = n_ghost_;
+        if (n_cols) *n_cols = n_cols_;
+    }
+    void mg_get_maps(int32_t* row_node, int32_t* col_unknown) override {
+        REQUIRE(have_mesh_, FEAB_ENOMESH, "mg_get_maps: no mesh");
+        CK(cudaSetDevice(device_));
+        if (row_node) CK(cudaMemcpy(row_node, node_of_col_p_, n_ * sizeof(int), cudaMemcpyDeviceToHost));
+        if (col_unknown) {
+            if (world_ > 1) {
+                CK(cudaMemcpy(col_unknown, d_glob_of_col_.p, n_cols_ * sizeof(int), cudaMemcpyDeviceToHost));
+            } else {
+                for (int64_t i = 0; i < n_cols_; i++) col_unknown[i] = (int32_t)i;
+            }
+        }
+    }
+
+    // ---------------------------------------------------------------- lock-step driving of virtual ranks
+    cudaStream_t ls_prepare(cudaStream_t shared) override {
+        require_ready_for_step();
+        REQUIRE(!use_bicgstab(), FEAB_EINVAL, "group_step: BiCGSTAB is not supported");
+        CK(cudaSetDevice(device_));
+        CK(cudaStreamSynchronize(stream_));
+        ls_stream_ = shared ? shared : stream_;
+        ensure_operator_on(ls_stream_);
+        return ls_stream_;
+    }
+    void ls_phase(int phase, int slot) override {
+        const R* A[2];
+        const R* dinv[2];
+        R* x[2];
+        solves(A, dinv, x);
+        cudaGraphConditionalHandle none = 0;
+        cudaStream_t s = ls_stream_;
+        switch (phase) {
+            case LS_PUSH_STATE: ph_push_state(s); break;
+            case LS_BEGIN: ph_step_begin(s, false); break;
+            case LS_COLLECT: ph_step_collect(s, false); break;
+            case LS_CG_BEGIN: ph_cg_begin(s, slot, x[slot], none, 0); launches_++; break;
+            case LS_SPMV: ph_spmv(s, slot, A[slot]); break;
+            case LS_UPDATE: ph_update(s, slot, dinv[slot], x[slot]); break;
+            case LS_DIRECTION: ph_direction(s, slot, dinv[slot], none, 0); launches_ += kernels_per_iteration(); break;
+            case LS_FINISH: ph_finish(s, false); break;
+            default: throw Err{FEAB_EINVAL, "ls_phase: bad phase"};
+        }
+        CK(cudaGetLastError());
+    }
+    int ls_num_solves() override { return eq_ == FEAB_EQ_REACTION_DIFFUSION ? 2 : 1; }
+    int ls_poll_done(int slot) override {
+        CK(cudaMemcpyAsync(h_flag_, &(d_st_ + slot)->done, sizeof(int), cudaMemcpyDeviceToHost, ls_stream_));
+        CK(cudaStreamSynchronize(ls_stream_));
+        return *h_flag_;
+    }
+    int64_t ls_maxit() override { return maxit(); }
+    void ls_finish_call(int nsteps) override {
+        CK(cudaStreamSynchronize(ls_stream_));
+        last_steps_ = nsteps;
+        last_ms_ = 0;
+        check_comm_error();
+    }
+    int device() const override { return device_; }
+
     int sms() const { return sms_; }
     const cudaDeviceProp& prop() const { return prop_; }
 
@@ -843,10 +1250,30 @@ class SolverT final : public SolverBase {
     DevBuf<float> d_xyz_, d_values_;
     DevBuf<uint32_t> d_tri_;
     DevBuf<uint8_t> d_onb_, d_advp_;
-    DevBuf<int> d_idx_, d_node_of_, d_rowptr_, d_col_, d_diag_, d_tpos_, d_smap_, d_cptr_, d_corner_;
+    DevBuf<int> d_idx_, d_node_of_, d_rowptr_, d_col_, d_diag_, d_smap_, d_cptr_, d_corner_;
     DevBuf<long long> d_scan_bsum_, d_scan_total_, d_brush_;
-    DevBuf<R> d_M_, d_K_, d_Adv_, d_Md_, d_A0_, d_A1_, d_dinv0_, d_dinv1_;
-    DevBuf<R> d_u_, d_v_, d_y_, d_r_[2], d_p_[2], d_w_[5], d_part_;
+    DevBuf<R> d_M_, d_K_, d_Adv_, d_AdvT_, d_Md_, d_A0_, d_A1_, d_dinv0_, d_dinv1_;
+    DevBuf<R> d_u_, d_v_, d_y_, d_r_[2], d_p_[2], d_w_[5], d_part_, d_rhs_tot_;
+
+    // ---- partition (world_ > 1; with world_ == 1 the maps alias idx_map / node_of) ----
+    int rank_ = 0, world_ = 1;
+    std::vector<int> h_part_;          // part of every mesh vertex (all ranks hold the same array)
+    bool part_given_ = false;
+    DevBuf<int> d_part_of_, d_rowmap_, d_colmap_, d_node_of_col_, d_glob_of_col_, d_send_rows_, d_send_nodes_;
+    const int* rowmap_p_ = nullptr;      // per node: local row or -1
+    const int* colmap_p_ = nullptr;      // per node: local column (row or ghost) or -1
+    const int* node_of_col_p_ = nullptr; // per local column: mesh node
+    int64_t nglob_ = 0;                  // unknowns of the whole mesh
+    int64_t n_int_ = 0, n_ghost_ = 0, ghost_base_ = 0, n_cols_ = 0;
+    DevBuf<unsigned char> d_arena_;      // CommCtrl | p[0] | p[1] | u | v | values  (peers map this allocation)
+    size_t off_vec_[5] = {0, 0, 0, 0, 0};
+    CommLocal* d_loc_ = nullptr;
+    Comm cm_;
+    HaloPlan hp_;
+    bool connected_[kMaxRanks] = {};
+    void* ipc_opened_[kMaxRanks] = {};
+    bool lockstep_ = false;
+    cudaStream_t ls_stream_ = nullptr;   // shared stream while driven phase by phase by feab_mg_group_step
     CgState<R>* d_st_ = nullptr;
     BicgState<R>* d_bst_ = nullptr;
     int* d_unstable_ = nullptr;
@@ -1056,6 +1483,61 @@ int feab_time_kernel(FeabHandle* h, int kernel, int reps, double* ms, double* by
     if (!ms || !bytes) return FEAB_EINVAL;
     FEAB_TRY(h, h->impl->time_kernel(kernel, reps, ms, bytes));
 }
+int feab_mg_config(FeabHandle* h, int rank, int world) { FEAB_TRY(h, h->impl->mg_config(rank, world)); }
+int feab_mg_set_partition(FeabHandle* h, const int32_t* part, int64_t V) { FEAB_TRY(h, h->impl->mg_set_partition(part, V)); }
+int feab_partition_rcb(int64_t V, const float* xyz, int parts, int32_t* part_out) {
+    if (V <= 0 || !xyz || parts < 1 || !part_out) return FEAB_EINVAL;
+    feab::rcb_partition(V, xyz, parts, part_out);
+    return FEAB_OK;
+}
+int feab_mg_export(FeabHandle* h, FeabMgExport* out) { FEAB_TRY(h, h->impl->mg_export(out)); }
+int feab_mg_connect(FeabHandle* h, int peer, const FeabMgExport* e, int same_process) { FEAB_TRY(h, h->impl->mg_connect(peer, e, same_process)); }
+int feab_mg_get_layout(FeabHandle* h, int64_t* n_own, int64_t* n_int, int64_t* n_ghost, int64_t* n_cols) {
+    FEAB_TRY(h, h->impl->mg_get_layout(n_own, n_int, n_ghost, n_cols));
+}
+int feab_mg_get_maps(FeabHandle* h, int32_t* row_node, int32_t* col_unknown) { FEAB_TRY(h, h->impl->mg_get_maps(row_node, col_unknown)); }
+
+static void group_step_impl(FeabHandle** hs, int count, int nsteps) {
+    FeabHandle* h0 = hs[0];
+    using B = feab::SolverBase;
+        for (int i = 1; i < count; i++)
+            if (hs[i]->impl->device() != h0->impl->device()) throw feab::Err{FEAB_EINVAL, "group_step: all handles must live on one device"};
+        // one stream for every virtual rank: stream order is the only synchronisation, no kernel ever spins
+        cudaStream_t s = h0->impl->ls_prepare(nullptr);
+        for (int i = 1; i < count; i++) hs[i]->impl->ls_prepare(s);
+        auto all = [&](int phase, int slot) {
+            for (int i = 0; i < count; i++) hs[i]->impl->ls_phase(phase, slot);
+        };
+        if (nsteps > 0) all(B::LS_PUSH_STATE, 0);
+        for (int st = 0; st < nsteps; st++) {
+            all(B::LS_BEGIN, 0);
+            all(B::LS_COLLECT, 0);
+            const int ns = h0->impl->ls_num_solves();
+            for (int slot = 0; slot < ns; slot++) {
+                all(B::LS_CG_BEGIN, slot);
+                const int64_t mi = h0->impl->ls_maxit();
+                const int batch = 8;
+                for (int64_t it = 0; it < mi + batch; it += batch) {
+                    for (int b = 0; b < batch; b++) {
+                        all(B::LS_SPMV, slot);
+                        all(B::LS_UPDATE, slot);
+                        all(B::LS_DIRECTION, slot);
+                    }
+                    if (h0->impl->ls_poll_done(slot)) break;
+                }
+            }
+            all(B::LS_FINISH, 0);
+        }
+        for (int i = 0; i < count; i++) hs[i]->impl->ls_finish_call(nsteps);
+}
+
+int feab_mg_group_step(FeabHandle** hs, int count, int nsteps) {
+    if (!hs || count < 1 || nsteps < 0) return FEAB_EINVAL;
+    for (int i = 0; i < count; i++)
+        if (!hs[i]) return FEAB_EINVAL;
+    FEAB_TRY(hs[0], group_step_impl(hs, count, nsteps));
+}
+
 int feab_device_info(const FeabHandle* h, int* sm_count, int64_t* total_mem, char* name64) {
     if (!h) return FEAB_EINVAL;
     if (sm_count) *sm_count = h->prop.multiProcessorCount;

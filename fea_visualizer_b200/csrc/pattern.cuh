@@ -117,37 +117,48 @@ __global__ void make_idx_map(const int* __restrict__ flag, const int* __restrict
 }
 
 // ------------------------------------------------------------------------------------------------
-// Row candidates: every triangle corner whose node is an unknown contributes its unknown partner nodes.
+// Row candidates: every triangle corner whose node owns a row contributes its unknown partner nodes.
 // An entry (i, j) of M/K exists iff some triangle holds both nodes and both pass the filter
 // (src/FEM/FEMContext.cpp:99, :136): with Dirichlet, boundary nodes have idx_map = -1, with Neumann all pass.
+// rowmap[node] = row owned by this handle (or -1), colmap[node] = column id (or -1).  On a single GPU both are
+// idx_map; on a partition (partition.cuh) rows are the owned unknowns and columns are owned + ghost unknowns.
 // ------------------------------------------------------------------------------------------------
-__global__ void count_row_candidates(const uint32_t* __restrict__ tri, int64_t T, const int* __restrict__ idx_map,
-                                     int* __restrict__ cnt) {
+__global__ void count_row_candidates(const uint32_t* __restrict__ tri, int64_t T, const int* __restrict__ rowmap,
+                                     const int* __restrict__ colmap, int* __restrict__ cnt) {
     int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= T) return;
-    int m[3];
-#pragma unroll
-    for (int i = 0; i < 3; i++) m[i] = idx_map[tri[3 * k + i]];
+    int rw[3], m[3];
 #pragma unroll
     for (int i = 0; i < 3; i++) {
-        if (m[i] < 0) continue;
+        uint32_t nd = tri[3 * k + i];
+        rw[i] = rowmap[nd];
+        m[i] = colmap[nd];
+    }
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+        if (rw[i] < 0) continue;
         int c = 1;  // the diagonal (i, i) is emitted by every triangle that holds an unknown node
         c += (m[(i + 1) % 3] >= 0) + (m[(i + 2) % 3] >= 0);
-        atomicAdd(&cnt[m[i]], c);
+        atomicAdd(&cnt[rw[i]], c);
     }
 }
-__global__ void fill_row_candidates(const uint32_t* __restrict__ tri, int64_t T, const int* __restrict__ idx_map,
-                                    const int* __restrict__ cand_ptr, int* __restrict__ fill, int* __restrict__ cand) {
+__global__ void fill_row_candidates(const uint32_t* __restrict__ tri, int64_t T, const int* __restrict__ rowmap,
+                                    const int* __restrict__ colmap, const int* __restrict__ cand_ptr, int* __restrict__ fill,
+                                    int* __restrict__ cand) {
     int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= T) return;
-    int m[3];
-#pragma unroll
-    for (int i = 0; i < 3; i++) m[i] = idx_map[tri[3 * k + i]];
+    int rw[3], m[3];
 #pragma unroll
     for (int i = 0; i < 3; i++) {
-        if (m[i] < 0) continue;
+        uint32_t nd = tri[3 * k + i];
+        rw[i] = rowmap[nd];
+        m[i] = colmap[nd];
+    }
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+        if (rw[i] < 0) continue;
         int c = 1 + (m[(i + 1) % 3] >= 0) + (m[(i + 2) % 3] >= 0);
-        int slot = cand_ptr[m[i]] + atomicAdd(&fill[m[i]], c);
+        int slot = cand_ptr[rw[i]] + atomicAdd(&fill[rw[i]], c);
         cand[slot++] = m[i];
         if (m[(i + 1) % 3] >= 0) cand[slot++] = m[(i + 1) % 3];
         if (m[(i + 2) % 3] >= 0) cand[slot++] = m[(i + 2) % 3];
@@ -213,66 +224,67 @@ __device__ __forceinline__ int find_in_row(const int* __restrict__ col, int b, i
 }
 
 // The precomputed CSR scatter map: for triangle k and local (i, j) the position of (row_i, col_j) in the
-// CSR value arrays, or -1 when the entry is filtered out.
-__global__ void build_scatter_map(const uint32_t* __restrict__ tri, int64_t T, const int* __restrict__ idx_map,
-                                  const int* __restrict__ rowptr, const int* __restrict__ col, int* __restrict__ smap) {
+// CSR value arrays, or -1 when the entry is filtered out (or the row belongs to another partition).
+__global__ void build_scatter_map(const uint32_t* __restrict__ tri, int64_t T, const int* __restrict__ rowmap,
+                                  const int* __restrict__ colmap, const int* __restrict__ rowptr, const int* __restrict__ col,
+                                  int* __restrict__ smap) {
     int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= T) return;
-    int m[3];
+    int rw[3], m[3];
 #pragma unroll
-    for (int i = 0; i < 3; i++) m[i] = idx_map[tri[3 * k + i]];
+    for (int i = 0; i < 3; i++) {
+        uint32_t nd = tri[3 * k + i];
+        rw[i] = rowmap[nd];
+        m[i] = colmap[nd];
+    }
 #pragma unroll
     for (int i = 0; i < 3; i++) {
         int b = 0, e = 0;
-        if (m[i] >= 0) {
-            b = rowptr[m[i]];
-            e = rowptr[m[i] + 1];
+        if (rw[i] >= 0) {
+            b = rowptr[rw[i]];
+            e = rowptr[rw[i] + 1];
         }
 #pragma unroll
         for (int j = 0; j < 3; j++) {
             int pos = -1;
-            if (m[i] >= 0 && m[j] >= 0) pos = find_in_row(col, b, e, m[j]);
+            if (rw[i] >= 0 && m[j] >= 0) pos = find_in_row(col, b, e, m[j]);
             smap[9 * k + 3 * i + j] = pos;
         }
     }
 }
 
-// Position of the transposed entry (the pattern is structurally symmetric), and whether the advection matrix
-// holds the entry: its filter drops every boundary node regardless of the boundary condition
-// (src/FEM/FEMContext.cpp:188).
-__global__ void build_transpose_map(const int* __restrict__ rowptr, const int* __restrict__ col, int64_t n,
-                                    const int* __restrict__ node_of, const uint8_t* __restrict__ on_boundary,
-                                    int* __restrict__ tpos, uint8_t* __restrict__ adv_present) {
+// Whether the advection matrix holds the entry: its filter drops every boundary node regardless of the
+// boundary condition (src/FEM/FEMContext.cpp:188).  node_of_col[c] = mesh node of column c (rows are the
+// first columns).
+__global__ void mark_adv_present(const int* __restrict__ rowptr, const int* __restrict__ col, int64_t n,
+                                 const int* __restrict__ node_of_col, const uint8_t* __restrict__ on_boundary,
+                                 uint8_t* __restrict__ adv_present) {
     int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= n) return;
-    bool rb = on_boundary[node_of[r]] != 0;
-    for (int k = rowptr[r]; k < rowptr[r + 1]; k++) {
-        int c = col[k];
-        tpos[k] = find_in_row(col, rowptr[c], rowptr[c + 1], (int)r);
-        adv_present[k] = (!rb && !on_boundary[node_of[c]]) ? 1 : 0;
-    }
+    bool rb = on_boundary[node_of_col[r]] != 0;
+    for (int k = rowptr[r]; k < rowptr[r + 1]; k++) adv_present[k] = (!rb && !on_boundary[node_of_col[col[k]]]) ? 1 : 0;
 }
 
 // ------------------------------------------------------------------------------------------------
 // Ordered adjacency for the deterministic assembly: per row, the incident triangle corners (3k + i) in
 // ascending order -- the order in which Eigen's collapseDuplicates sums the triplets of an entry.
 // ------------------------------------------------------------------------------------------------
-__global__ void count_row_corners(const uint32_t* __restrict__ tri, int64_t T, const int* __restrict__ idx_map, int* __restrict__ cnt) {
+__global__ void count_row_corners(const uint32_t* __restrict__ tri, int64_t T, const int* __restrict__ rowmap, int* __restrict__ cnt) {
     int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= T) return;
 #pragma unroll
     for (int i = 0; i < 3; i++) {
-        int m = idx_map[tri[3 * k + i]];
+        int m = rowmap[tri[3 * k + i]];
         if (m >= 0) atomicAdd(&cnt[m], 1);
     }
 }
-__global__ void fill_row_corners(const uint32_t* __restrict__ tri, int64_t T, const int* __restrict__ idx_map,
+__global__ void fill_row_corners(const uint32_t* __restrict__ tri, int64_t T, const int* __restrict__ rowmap,
                                  const int* __restrict__ cptr, int* __restrict__ fill, int* __restrict__ corner) {
     int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= T) return;
 #pragma unroll
     for (int i = 0; i < 3; i++) {
-        int m = idx_map[tri[3 * k + i]];
+        int m = rowmap[tri[3 * k + i]];
         if (m >= 0) corner[cptr[m] + atomicAdd(&fill[m], 1)] = (int)(3 * k + i);
     }
 }

@@ -8,6 +8,7 @@
 // Grid-wide reductions are deterministic: every CTA writes one partial, the consumer kernel re-sums the
 // partials in a fixed order (no atomics, no host round trip).
 #pragma once
+#include "comm.cuh"
 #include "common.cuh"
 
 namespace feab {
@@ -42,10 +43,10 @@ __device__ __forceinline__ R ld_stream(const R* p) {
 // CPUSolver::get_surface_value_vector (src/FEM/CPUSolver.cpp:13-21)
 // ------------------------------------------------------------------------------------------------
 template <typename R>
-__global__ void gather_values(const float* __restrict__ values, const int* __restrict__ idx_map, int64_t V, R* __restrict__ x) {
+__global__ void gather_values(const float* __restrict__ values, const int* __restrict__ colmap, int64_t V, R* __restrict__ x) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < V) {
-        int m = idx_map[i];
+        int m = colmap[i];  // idx_map on one GPU; owned + ghost columns on a partition
         if (m >= 0) x[m] = (R)values[i];
     }
 }
@@ -61,7 +62,7 @@ __global__ void gather_values(const float* __restrict__ values, const int* __res
 template <typename R>
 __global__ void __launch_bounds__(kBlock) build_operator(int eq, int transposed, int64_t nnz, const R* __restrict__ Mv,
                                                           const R* __restrict__ Kv, const R* __restrict__ Av,
-                                                          const int* __restrict__ tpos, StepScalars sc, R* __restrict__ Md,
+                                                          const R* __restrict__ AvT, StepScalars sc, R* __restrict__ Md,
                                                           R* __restrict__ A0, R* __restrict__ A1) {
     using O = Ops<R>;
     const R dt = (R)sc.dt, c0 = (R)sc.c0, c1 = (R)sc.c1;
@@ -75,7 +76,7 @@ __global__ void __launch_bounds__(kBlock) build_operator(int eq, int transposed,
             R cc = O::mul(c0, c0);
             A0[k] = O::add(md, O::mul(O::mul(cc, kv), dt));
         } else if (eq == 2) {
-            R a = transposed ? Av[tpos[k]] : Av[k];
+            R a = transposed ? AvT[k] : Av[k];
             A0[k] = O::sub(O::add(md, O::mul(c0, kv)), a);
         } else {
             A0[k] = O::add(md, O::mul(c0, kv));
@@ -240,11 +241,18 @@ template <typename R>
 __global__ void __launch_bounds__(kBlock) cg_update(R* __restrict__ x, R* __restrict__ r, const R* __restrict__ p,
                                                     const R* __restrict__ y, const R* __restrict__ dinv, int64_t n,
                                                     CgState<R>* __restrict__ st, const R* __restrict__ part_pap, int n_part,
-                                                    R* __restrict__ part_rr, R* __restrict__ part_rz) {
+                                                    R* __restrict__ part_rr, R* __restrict__ part_rz, Comm cm) {
     using O = Ops<R>;
     __shared__ R red[kBlock / 32 + 1];
     if (st->done) return;
-    const R pap = sum_partials<R>(part_pap, n_part, red);
+    R pap;
+    if (cm.world > 1) {
+        R t[1];
+        ar_consume<R, 1>(cm, t);
+        pap = t[0];
+    } else {
+        pap = sum_partials<R>(part_pap, n_part, red);
+    }
     const int it = st->iter1;
     const R alpha = st->abs_new[(it - 1) & 1] / pap;
     constexpr int N = Vec<R>::N;
@@ -286,6 +294,10 @@ __global__ void __launch_bounds__(kBlock) cg_update(R* __restrict__ x, R* __rest
         part_rr[blockIdx.x] = rr;
         part_rz[blockIdx.x] = rz;
     }
+    if (cm.world > 1) {
+        __syncthreads();
+        ar_publish<R, 2>(cm, part_rr, (int)(part_rz - part_rr), red);
+    }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -297,15 +309,23 @@ template <typename R>
 __global__ void __launch_bounds__(kBlock) cg_direction(const R* __restrict__ r, R* __restrict__ p, const R* __restrict__ dinv,
                                                        int64_t n, CgState<R>* __restrict__ st, const R* __restrict__ part_rr,
                                                        const R* __restrict__ part_rz, int n_part,
-                                                       cudaGraphConditionalHandle cond, int use_cond) {
+                                                       cudaGraphConditionalHandle cond, int use_cond, Comm cm) {
     using O = Ops<R>;
     __shared__ R red[kBlock / 32 + 1];
     if (st->done) {
         if (use_cond && blockIdx.x == 0 && threadIdx.x == 0) cudaGraphSetConditional(cond, 0);
         return;
     }
-    const R rr = sum_partials<R>(part_rr, n_part, red);
-    const R rz = sum_partials<R>(part_rz, n_part, red);
+    R rr, rz;
+    if (cm.world > 1) {
+        R t[2];
+        ar_consume<R, 2>(cm, t);
+        rr = t[0];
+        rz = t[1];
+    } else {
+        rr = sum_partials<R>(part_rr, n_part, red);
+        rz = sum_partials<R>(part_rz, n_part, red);
+    }
     const int it = st->iter1;
     const bool conv = rr < st->thr;
     const R abs_old = st->abs_new[(it - 1) & 1];
@@ -382,7 +402,7 @@ __global__ void __launch_bounds__(kBlock) rhs_init(const int* __restrict__ rowpt
                                                    const R* __restrict__ v, const R* __restrict__ dinv0,
                                                    const R* __restrict__ dinv1, int64_t n, int num_tiles, StepScalars sc,
                                                    R* __restrict__ r0, R* __restrict__ p0, R* __restrict__ r1, R* __restrict__ p1,
-                                                   R* __restrict__ part /* 4 x gridDim.x: bb0, rz0, bb1, rz1 */) {
+                                                   R* __restrict__ part /* 4 x gridDim.x: bb0, rz0, bb1, rz1 */, Comm cm) {
     using O = Ops<R>;
     extern __shared__ __align__(16) unsigned char smraw[];
     R* prod0 = reinterpret_cast<R*>(smraw);
@@ -475,6 +495,10 @@ __global__ void __launch_bounds__(kBlock) rhs_init(const int* __restrict__ rowpt
             part[3 * gridDim.x + blockIdx.x] = rz1;
         }
     }
+    if (cm.world > 1) {
+        __syncthreads();
+        ar_publish<R, (EQ == 3 ? 4 : 2)>(cm, part, (int)gridDim.x, red);
+    }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -483,12 +507,12 @@ __global__ void __launch_bounds__(kBlock) rhs_init(const int* __restrict__ rowpt
 // sol_is_v: Gray-Scott writes v back to the surface (:144); the other equations write u.
 // ------------------------------------------------------------------------------------------------
 template <typename R>
-__global__ void finish_step(float* __restrict__ values, const int* __restrict__ idx_map, int64_t V, R* __restrict__ u,
-                            R* __restrict__ v, int wave, R dt, int sol_is_v, int* __restrict__ unstable) {
+__global__ void finish_step(float* __restrict__ values, const int* __restrict__ idx_map, const int* __restrict__ rowmap, int64_t V,
+                            R* __restrict__ u, R* __restrict__ v, int wave, R dt, int sol_is_v, int* __restrict__ unstable) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     bool bad = false;
     if (i < V) {
-        int m = idx_map[i];
+        int m = rowmap[i];  // == idx_map on one GPU; on a partition only the owned nodes are written
         if (m >= 0) {
             R ui = u[m], vi = v[m];
             if (wave) {
@@ -497,7 +521,7 @@ __global__ void finish_step(float* __restrict__ values, const int* __restrict__ 
             }
             values[i] = (float)(sol_is_v ? vi : ui);
             bad = ui > (R)1e4f || vi > (R)1e4f;
-        } else {
+        } else if (idx_map[i] < 0) {
             values[i] = 0.0f;
         }
     }

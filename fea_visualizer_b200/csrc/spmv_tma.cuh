@@ -50,21 +50,6 @@ __device__ __forceinline__ void l2_prefetch(const void* src_gmem, uint32_t bytes
     asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src_gmem), "r"(bytes) : "memory");
 }
 
-template <typename T, int NW>
-__device__ __forceinline__ T block_sum_n(T v, T* sm /* NW + 1 */) {
-    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    v = warp_sum(v);
-    if (lane == 0) sm[w] = v;
-    __syncthreads();
-    if (w == 0) {
-        T t = lane < NW ? sm[lane] : T(0);
-        t = warp_sum(t);
-        if (lane == 0) sm[NW] = t;
-    }
-    __syncthreads();
-    return sm[NW];
-}
-
 // Geometry of one pipeline configuration.  CPR = staged entries per row of capacity (tiles with more entries
 // fall back to direct global loads for that tile).
 template <typename R, int ROWS, int CPR, int STAGES>
@@ -85,7 +70,8 @@ constexpr int kTmaPad = 16;
 template <typename R, int ROWS, int CPR, int STAGES, int MINB>
 __global__ void __launch_bounds__(ROWS, MINB)
     spmv_dot_tma(const int* __restrict__ rowptr, const int* __restrict__ col, const R* __restrict__ val, const R* __restrict__ x,
-                 R* __restrict__ y, int64_t n, int num_tiles, CgState<R>* __restrict__ st, R* __restrict__ part_pap, int prefetch_x) {
+                 R* __restrict__ y, int64_t n, int num_tiles, CgState<R>* __restrict__ st, R* __restrict__ part_pap, int prefetch_x,
+                 Comm cm, HaloPlan hp, int first_halo_tile) {
     using Cfg = TmaCfg<R, ROWS, CPR, STAGES>;
     extern __shared__ unsigned char smraw_tma[];
     unsigned char* base = reinterpret_cast<unsigned char*>(((uintptr_t)smraw_tma + 127) & ~(uintptr_t)127);
@@ -130,7 +116,14 @@ __global__ void __launch_bounds__(ROWS, MINB)
 
     R acc = (R)0;
     int i = 0;
+    bool halo_ok = cm.world == 1;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, i++) {
+        if (!halo_ok && tile >= first_halo_tile) {
+            // partitioned solve: rows from here on read ghost columns -- wait for the neighbours' pushes (comm.cuh)
+            if (threadIdx.x == 0) wait_flags(cm, hp, 0, *(volatile unsigned long long*)&cm.loc->halo_seq);
+            __syncthreads();
+            halo_ok = true;
+        }
         const int s = i % STAGES;
         const uint32_t parity = (uint32_t)((i / STAGES) & 1);
         mbar_wait(&full[s], parity);
@@ -205,6 +198,10 @@ __global__ void __launch_bounds__(ROWS, MINB)
     if (threadIdx.x == 0) {
         part_pap[blockIdx.x] = acc;
         if (blockIdx.x == 0 && st != nullptr) st->iter1 += 1;
+    }
+    if (cm.world > 1) {
+        __syncthreads();
+        ar_publish<R, 1, ROWS / 32>(cm, part_pap, 0, red);
     }
 }
 

@@ -26,7 +26,8 @@ ABI_SYMBOLS = [
     "feab_get_counts", "feab_get_idx_map", "feab_get_csr", "feab_set_equation", "feab_set_params", "feab_get_params",
     "feab_set_solver_options", "feab_get_solver_options", "feab_clear", "feab_set_values", "feab_get_values", "feab_brush",
     "feab_step", "feab_unstable", "feab_last_stats", "feab_get_state", "feab_set_state", "feab_time_kernel",
-    "feab_device_info",
+    "feab_device_info", "feab_mg_config", "feab_mg_set_partition", "feab_partition_rcb", "feab_mg_export", "feab_mg_connect",
+    "feab_mg_get_layout", "feab_mg_get_maps", "feab_mg_group_step",
 ]
 
 
@@ -42,6 +43,12 @@ class FeabSolverOptions(C.Structure):
 class FeabStats(C.Structure):
     _fields_ = [("iterations", C.c_int64 * 2), ("rel_residual", C.c_double * 2), ("last_call_ms", C.c_double),
                 ("last_call_steps", C.c_int64), ("kernel_launches", C.c_int64), ("solve_ms", C.c_double)]
+
+
+class FeabMgExport(C.Structure):
+    _fields_ = [("ipc_handle", C.c_ubyte * 64), ("base_ptr", C.c_uint64), ("arena_bytes", C.c_uint64), ("off_vec", C.c_uint64 * 5),
+                ("n_own", C.c_int64), ("n_ghost", C.c_int64), ("ghost_base", C.c_int64), ("num_nodes", C.c_int64),
+                ("rank", C.c_int32), ("world", C.c_int32), ("device", C.c_int32), ("pid", C.c_int32)]
 
 
 class FeabError(RuntimeError):
@@ -225,3 +232,52 @@ class Feab:
         name = C.create_string_buffer(64)
         self._ck(self.lib.feab_device_info(self.h, C.byref(sm), C.byref(mem), name))
         return {"sm_count": sm.value, "total_mem": mem.value, "name": name.value.decode()}
+
+    # -- partitioned (multi-GPU) solve --
+    def mg_config(self, rank, world):
+        self._ck(self.lib.feab_mg_config(self.h, C.c_int(rank), C.c_int(world)))
+
+    def mg_set_partition(self, part):
+        part = np.ascontiguousarray(part, dtype=np.int32)
+        self._ck(self.lib.feab_mg_set_partition(self.h, C.c_void_p(part.ctypes.data), C.c_int64(part.shape[0])))
+
+    def mg_export(self) -> bytes:
+        e = FeabMgExport()
+        self._ck(self.lib.feab_mg_export(self.h, C.byref(e)))
+        return bytes(e)
+
+    def mg_connect(self, peer_rank, blob: bytes, same_process=False):
+        e = FeabMgExport.from_buffer_copy(blob)
+        self._ck(self.lib.feab_mg_connect(self.h, C.c_int(peer_rank), C.byref(e), C.c_int(1 if same_process else 0)))
+
+    def mg_layout(self):
+        a, b, c, d = C.c_int64(), C.c_int64(), C.c_int64(), C.c_int64()
+        self._ck(self.lib.feab_mg_get_layout(self.h, C.byref(a), C.byref(b), C.byref(c), C.byref(d)))
+        return {"n_own": a.value, "n_interior": b.value, "n_ghost": c.value, "n_cols": d.value}
+
+    def mg_maps(self):
+        lay = self.mg_layout()
+        row_node = np.empty(max(lay["n_own"], 1), dtype=np.int32)
+        col_unknown = np.empty(max(lay["n_cols"], 1), dtype=np.int32)
+        self._ck(self.lib.feab_mg_get_maps(self.h, C.c_void_p(row_node.ctypes.data), C.c_void_p(col_unknown.ctypes.data)))
+        return row_node[:lay["n_own"]], col_unknown[:lay["n_cols"]]
+
+
+def partition_rcb(xyz, parts):
+    """Recursive coordinate bisection (host C++, csrc/partition.cuh); needs no GPU."""
+    lib = load_library()
+    xyz = np.ascontiguousarray(xyz, dtype=np.float32)
+    out = np.empty(xyz.shape[0], dtype=np.int32)
+    rc = lib.feab_partition_rcb(C.c_int64(xyz.shape[0]), C.c_void_p(xyz.ctypes.data), C.c_int(parts), C.c_void_p(out.ctypes.data))
+    if rc != 0:
+        raise FeabError(rc, "feab_partition_rcb: bad arguments")
+    return out
+
+
+def group_step(handles, nsteps=1):
+    """Lock-step advance of several partitioned handles living on one device in this process (virtual ranks)."""
+    lib = load_library()
+    arr = (C.c_void_p * len(handles))(*[h.h for h in handles])
+    rc = lib.feab_mg_group_step(arr, C.c_int(len(handles)), C.c_int(nsteps))
+    if rc != 0:
+        raise FeabError(rc, lib.feab_last_error(handles[0].h).decode())

@@ -49,7 +49,8 @@ enum {
     FEAB_EINVAL = -1,   /* bad argument / call order */
     FEAB_ENOMESH = -2,  /* no mesh set */
     FEAB_ENOGPU = -3,   /* no CUDA device: there is no CPU fallback */
-    FEAB_ENOMEM = -4
+    FEAB_ENOMEM = -4,
+    FEAB_ECOMM = -5     /* partitioned solve: a peer never answered (bounded device-side wait expired) */
 };
 
 /* include/FEM/EquationParameters.hpp:4-49.  Scalars keep the reference's float type; they are promoted to
@@ -136,6 +137,43 @@ int feab_last_stats(FeabHandle* h, FeabStats* out);
 /* CPUSolver's private u (which = 0) / v (which = 1), length num_unknowns, handle's real type */
 int feab_get_state(FeabHandle* h, int which, void* out);
 int feab_set_state(FeabHandle* h, int which, const void* in);
+
+/* -- partitioned (multi-GPU) solve: SURVEY.md 8(e) ------------------------------------------------
+ * One handle per GPU ("rank"), all holding the SAME mesh; rows are partitioned over the ranks, every rank
+ * assembles and solves its own rows, halo values and dot products travel through peer memory over NVLink inside
+ * the solver's kernels.  Call order per rank:
+ *   feab_create; feab_mg_config(rank, world); [feab_mg_set_partition]; feab_set_mesh (all ranks, same arrays);
+ *   feab_mg_export -> exchange the FeabMgExport blobs between the ranks (any transport; bytes) ->
+ *   feab_mg_connect for every peer; then feab_step as usual, all ranks calling it with the same arguments.
+ * feab_set_mesh / feab_set_boundary_condition re-allocate the exported arena: export + connect again afterwards.
+ * The reference has no counterpart (single process, single thread); the data contract through surface->values is
+ * kept: after feab_step(values, n, sync=1) every rank's values array is complete. */
+typedef struct {
+    unsigned char ipc_handle[64]; /* cudaIpcMemHandle_t of the arena */
+    uint64_t base_ptr;            /* device address in the exporting process (same-process connection) */
+    uint64_t arena_bytes;
+    uint64_t off_vec[5];          /* byte offsets of p[0], p[1], u, v, values inside the arena */
+    int64_t n_own, n_ghost, ghost_base, num_nodes;
+    int32_t rank, world, device, pid;
+} FeabMgExport;
+
+/* Must precede feab_set_mesh.  world <= 8. */
+int feab_mg_config(FeabHandle* h, int rank, int world);
+/* Optional: part[v] in [0, world) for every mesh vertex, identical on all ranks.  Default: recursive coordinate
+ * bisection of the vertex coordinates (feab_partition_rcb), computed inside feab_set_mesh. */
+int feab_mg_set_partition(FeabHandle* h, const int32_t* part, int64_t num_vertices);
+int feab_partition_rcb(int64_t num_vertices, const float* xyz, int parts, int32_t* part_out);
+int feab_mg_export(FeabHandle* h, FeabMgExport* out);
+int feab_mg_connect(FeabHandle* h, int peer_rank, const FeabMgExport* peer, int same_process);
+/* Local layout: rows [0, n_interior) touch no ghost column; columns are [rows | padding | ghosts], n_cols in all. */
+int feab_mg_get_layout(FeabHandle* h, int64_t* n_own, int64_t* n_interior, int64_t* n_ghost, int64_t* n_cols);
+/* row_node[n_own]: mesh node of every local row; col_unknown[n_cols]: global unknown id (idx_map numbering) of every
+ * local column, -1 for padding.  With these, feab_get_csr / feab_get_state of a rank can be placed in the global system. */
+int feab_mg_get_maps(FeabHandle* h, int32_t* row_node, int32_t* col_unknown);
+/* Test driver: advances `count` handles that live in THIS process on ONE device ("virtual ranks") in lock-step,
+ * phase by phase on one stream, so that no kernel ever waits for a kernel that has not been launched yet.  Exercises
+ * the partitioned data path (numbering, halo pushes, mailbox all-reduce) without `count` GPUs. */
+int feab_mg_group_step(FeabHandle** handles, int count, int nsteps);
 
 /* -- measurement hooks (used by bench.py; not part of the reference interface) ---------------- */
 /* Runs `reps` launches of one hot kernel on the current operator and returns the mean device time per

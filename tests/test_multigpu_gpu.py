@@ -1,0 +1,165 @@
+"""Partitioned (multi-GPU) solve, SURVEY.md 8(e), exercised with VIRTUAL RANKS: P partitioned handles on one B200,
+advanced in lock-step (feab_mg_group_step).  Same numbering, kernels, halo pushes and mailbox all-reduces as the
+one-process-per-GPU run; only the waiting is replaced by stream order.  Bars: layout / pattern / index work bit-exact;
+fields vs the single-GPU solver within reduction-order tolerance (1e-11), vs the fp64 oracle within 1e-8 per step.
+"""
+import numpy as np
+import pytest
+
+from fea_visualizer_b200 import feab, meshes
+from fea_visualizer_b200.multigpu import VirtualRanks
+from oracle import oracle as O
+from tests.util import rel_l2, run_steps
+
+pytestmark = pytest.mark.gpu
+
+
+def mesh(name):
+    if name == "ico12":
+        xyz, tri = meshes.icosphere(12)
+    elif name == "ico8d":
+        xyz, tri = meshes.icosphere(8, displace=True)
+    elif name == "disk14":
+        xyz, tri = meshes.disk(14)
+    else:
+        xyz, tri = meshes.grid(15, 11)
+    return xyz, tri, meshes.boundary_flags(len(xyz), tri)
+
+
+def single(real, xyz, tri, ob, bc, **solver):
+    F = feab.Feab(real=real)
+    F.set_boundary_condition(bc)
+    if solver:
+        F.set_solver(**solver)
+    F.set_mesh(xyz, tri, ob)
+    return F
+
+
+def virtual(world, real, xyz, tri, ob, bc, part=None, **solver):
+    G = VirtualRanks(world, real=real, part=part, **solver)
+    for h in G.hs:
+        h.set_boundary_condition(bc)
+    G.set_mesh(xyz, tri, ob)
+    return G
+
+
+@pytest.mark.parametrize("name,bc", [("ico12", 0), ("disk14", 0), ("disk14", 1), ("grid", 0)])
+@pytest.mark.parametrize("world", [2, 3, 8])
+def test_partition_layout_and_matrices(name, bc, world):
+    xyz, tri, ob = mesh(name)
+    F = single(64, xyz, tri, ob, bc, assembly=feab.ASSEMBLY_ORDERED)
+    G = virtual(world, 64, xyz, tri, ob, bc, assembly=feab.ASSEMBLY_ORDERED)
+    idx = F.idx_map()
+    n = F.num_unknowns()
+    part = feab.partition_rcb(xyz, world)
+    seen = np.zeros(len(xyz), int)
+    for r, (h, (row_node, col_unknown)) in enumerate(zip(G.hs, G.rows)):
+        lay = h.mg_layout()
+        assert (h.idx_map() == idx).all()
+        seen[row_node] += 1
+        assert (part[row_node] == r).all() and (idx[row_node] >= 0).all()            # rows = the unknowns this rank owns
+        assert lay["n_own"] == len(row_node) and lay["n_cols"] == len(col_unknown)
+        # interior rows first, each group in ascending global order
+        g = idx[row_node]
+        ni = lay["n_interior"]
+        assert (np.diff(g[:ni]) > 0).all() and (np.diff(g[ni:]) > 0).all()
+        # ghost columns belong to other ranks; interior rows never touch them
+        ghosts = col_unknown[lay["n_own"]:]
+        ghosts = ghosts[ghosts >= 0]
+        assert len(ghosts) == lay["n_ghost"]
+        node_of = np.flatnonzero(idx >= 0)
+        assert (part[node_of[ghosts]] != r).all()
+        rowptr, col, _ = h.csr(0)
+        if ni:
+            assert col[:rowptr[ni]].max() < lay["n_own"]
+        assert (np.diff(np.concatenate([col[rowptr[i]:rowptr[i + 1]] for i in range(min(50, len(row_node)))])) != 0).all()
+    assert (seen[idx >= 0] == 1).all() and (seen[idx < 0] == 0).all()               # every unknown owned exactly once
+    # the global matrices assembled from the pieces are the single-GPU matrices, bit for bit
+    for which in range(3):
+        rowptr, col, val = F.csr(which)
+        A = np.zeros((n, n))
+        P = np.zeros((n, n), bool)
+        rows = np.repeat(np.arange(n), np.diff(rowptr))
+        A[rows, col] = val
+        P[rows, col] = True
+        GA, GP = G.global_csr_dense(which)
+        assert (GP == P).all(), which
+        assert (GA == A).all(), which
+
+
+@pytest.mark.parametrize("name,bc", [("ico12", 0), ("disk14", 0), ("disk14", 1)])
+@pytest.mark.parametrize("world", [2, 4, 7])
+@pytest.mark.parametrize("eq", [0, 1, 2, 3])
+def test_virtual_ranks_step_parity(name, bc, world, eq):
+    xyz, tri, ob = mesh(name)
+    V = len(xyz)
+    F = single(64, xyz, tri, ob, bc)
+    G = virtual(world, 64, xyz, tri, ob, bc)
+    D = O.Oracle(xyz, tri, ob, bc, real=64)
+    ref = []
+    run_steps(F, V, eq, 5, per_step=lambda s, X: ref.append((X.get_values(), X.get_state(0), X.get_state(1), X.stats()["iterations"])))
+    orc = []
+    run_steps(D, V, eq, 5, per_step=lambda s, X: orc.append((X.get_values(), X.get_state(0), X.get_state(1))))
+    worst = [0.0, 0.0]
+
+    def check(s, X):
+        v, u, vv, it = ref[s]
+        worst[0] = max(worst[0], rel_l2(X.get_values(), v), rel_l2(X.get_state(0), u), rel_l2(X.get_state(1), vv))
+        worst[1] = max(worst[1], rel_l2(X.get_values(), orc[s][0]), rel_l2(X.get_state(0), orc[s][1]), rel_l2(X.get_state(1), orc[s][2]))
+        git = X.stats()["iterations"]
+        assert abs(git[0] - it[0]) <= 2 and abs(git[1] - it[1]) <= 2, (git, it)
+
+    run_steps(G, V, eq, 5, per_step=check)
+    assert worst[0] <= 1e-11, worst      # vs single GPU: summation order only
+    assert worst[1] <= 1e-8, worst       # vs the fp64 oracle: the north star's per-step bar
+    assert G.unstable() == F.unstable()
+
+
+def test_worst_case_partition_every_row_is_boundary():
+    """part = node % P: no interior rows at all, every neighbour pair exchanges halos."""
+    xyz, tri, ob = mesh("ico8d")
+    V = len(xyz)
+    part = (np.arange(V) % 4).astype(np.int32)
+    G = virtual(4, 64, xyz, tri, ob, 0, part=part)
+    assert all(h.mg_layout()["n_interior"] == 0 for h in G.hs)
+    F = single(64, xyz, tri, ob, 0)
+    for eq in (0, 3):
+        a = run_steps(F, V, eq, 4)
+        b = run_steps(G, V, eq, 4)
+        assert rel_l2(b, a) <= 1e-6          # values are float32
+        assert rel_l2(G.get_state(0), F.get_state(0)) <= 1e-11
+
+
+def test_virtual_ranks_fp32_and_multi_step_call():
+    xyz, tri, ob = mesh("ico12")
+    V = len(xyz)
+    F = single(32, xyz, tri, ob, 0)
+    G = virtual(3, 32, xyz, tri, ob, 0)
+    a = run_steps(F, V, 3, 5)
+    b = run_steps(G, V, 3, 5)
+    assert rel_l2(b, a) <= 5e-6
+    # several steps inside one call == the same steps one by one (state halos are pushed between steps)
+    v0 = np.zeros(V, np.float32)
+    v0[meshes.seed_nodes(V)] = 1.0
+    ordered = dict(assembly=feab.ASSEMBLY_ORDERED)     # scatter assembly sums the diagonal in atomic arrival order
+    A, B = virtual(2, 64, xyz, tri, ob, 0, **ordered), virtual(2, 64, xyz, tri, ob, 0, **ordered)
+    for X in (A, B):
+        X.set_equation(1)
+        X.set_values(v0)
+    A.step(4)
+    for _ in range(4):
+        B.step(1)
+    assert (A.get_state(0) == B.get_state(0)).all() and (A.get_state(1) == B.get_state(1)).all()
+
+
+def test_unconnected_partition_and_bicgstab_are_refused():
+    xyz, tri, ob = mesh("grid")
+    h = feab.Feab(real=64)
+    h.mg_config(0, 2)
+    h.set_mesh(xyz, tri, ob)
+    with pytest.raises(feab.FeabError):
+        h.step(1)
+    G = virtual(2, 64, xyz, tri, ob, 0, solver=feab.SOLVER_BICGSTAB)
+    G.set_equation(2)
+    with pytest.raises(feab.FeabError):
+        G.step(1)
