@@ -226,18 +226,25 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     torch.cuda.set_device(local_rank)
 
-    # weak scaling over independent replicas of the mesh until the partitioned solver lands (DESIGN.md section e)
+    # N > 1: ONE mesh, rows partitioned over the ranks (RCB), halos and dot products through peer memory inside the
+    # solver kernels -> strong scaling of the metric's 16 M-vertex mesh
     xyz, tri, ob = build_mesh(args.nu)
     V = len(xyz)
     F = feab.Feab(real=args.real, device=local_rank)
+    if world > 1:
+        F.mg_config(rank, world)
     if args.tol >= 0:
         F.set_solver(tolerance=args.tol)
     if args.loop == "host":
         F.set_solver(loop_mode=feab.LOOP_HOST_BATCHED)
     t0 = time.perf_counter()
     F.set_mesh(xyz, tri, ob)
+    if world > 1:
+        from fea_visualizer_b200.multigpu import connect_ranks
+        connect_ranks(F, dist)
     setup_s = time.perf_counter() - t0
-    _, n, nnz, max_row = F.counts()
+    _, n, nnz, max_row = F.counts()           # this rank's rows / entries
+    lay = F.mg_layout()
     F.set_equation(EQ_GS)
     F.set_params(EQ_GS, GS["dt"], GS["Du"], GS["Dv"], GS["f"], GS["k"])
     F.clear()
@@ -276,15 +283,22 @@ def main():
     clocks = sampler.stop() if rank == 0 else None
 
     t = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
+    tot = torch.tensor([n, nnz, lay["n_ghost"], launches], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tot)
     ms_max, e2e_ms_max = t.tolist()
+    n_all, nnz_all, ghosts_all, launches_all = (int(x) for x in tot.tolist())
+    rb = 8 if args.real == 64 else 4
+    # algorithmic bytes of one Gray-Scott step: fused RHS + (it_u + it_v) PCG iterations
+    it_bytes_row = nnz_all / n_all * (rb + 4) + 4 + 13 * rb
+    step_bytes = nnz_all * (rb + 4) + 4 * n_all + 8 * n_all * rb + (its[0] + its[1]) * it_bytes_row * n_all
 
     # --- roofline of the dominant kernel (SpMV + dot), measured live with CUDA events on the solver stream ---
     roof = None
     kernels = {}
-    if rank == 0:
-        peak, peak_src = measured_peak()
+    peak, peak_src = measured_peak()
+    if rank == 0 and world == 1:
         for kid, name in ((0, "spmv_dot"), (1, "cg_update"), (2, "cg_direction"), (3, "rhs_init")):
             kms, kbytes = F.time_kernel(kid, 20)
             kernels[name] = {"ms": kms, "algorithmic_bytes": kbytes, "GBps": kbytes / kms / 1e6}
@@ -296,7 +310,18 @@ def main():
                 "traffic_source": "profiles/r01_spmv_traffic.json (ncu --set full, per launch)", "peak_source": peak_src, "frac_of_nominal_8TBps": k0["GBps"] / 8000.0,
                 "pcg_iteration": {"ms": it_ms, "algorithmic_bytes": it_bytes, "GBps": it_bytes / it_ms / 1e6,
                                   "frac": it_bytes / it_ms / 1e6 / peak},
+                "whole_step": {"algorithmic_bytes": step_bytes, "GBps": step_bytes / (ms_max / args.steps) / 1e6,
+                               "frac": step_bytes / (ms_max / args.steps) / 1e6 / peak},
                 "kernels": kernels}
+    elif rank == 0:
+        # partitioned run: the solver kernels wait for their peers, so no kernel is timed alone; the figure is the
+        # whole step (RHS + all PCG iterations, halo waits and all-reduce latency included) per GPU
+        gbps = step_bytes / (ms_max / args.steps) / 1e6 / world
+        roof = {"bound": "hbm", "kernel": "whole Gray-Scott step (rhs_init + PCG iterations), per GPU", "achieved": gbps, "peak": peak,
+                "unit": "GB/s", "frac": gbps / peak, "traffic": None, "algorithmic_bytes": step_bytes / world, "peak_source": peak_src,
+                "frac_of_nominal_8TBps": gbps / 8000.0,
+                "halo": {"ghost_columns_total": ghosts_all, "bytes_per_iteration_total": ghosts_all * rb,
+                         "allreduces_per_iteration": 2, "collective": "P2P stores + mailbox flags over NVLink inside the solver kernels"}}
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
@@ -307,17 +332,18 @@ def main():
                              f"{args.cpu_steps} steps, fp32 Eigen PCG tol 1.19e-7), converted by {res['conversion']}; {res['build']}"}
 
     if rank == 0:
-        total_steps = args.steps * world      # replicas: every rank advances its own mesh
+        total_steps = args.steps              # one mesh: N ranks advance the same time step together
         value = total_steps / (ms_max / 1e3)
         line = {"metric": "gray_scott_timesteps_per_s", "value": value, "unit": "steps/s", "n_gpus": world, "steps": args.steps,
-                "warmup": max(args.warmup, 3), "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak",
-                "vs_baseline": None, "dtype": "f64" if args.real == 64 else "f32", "data": "synthetic",
-                "config": {"workload": workload, "rows": n, "nnz": nnz, "max_row": max_row, "parallelism": f"replicas x{world}",
+                "warmup": max(args.warmup, 3), "ms_per_step": ms_max / args.steps, "higher_is_better": True,
+                "scaling": "strong" if world > 1 else "weak", "vs_baseline": None, "dtype": "f64" if args.real == 64 else "f32", "data": "synthetic",
+                "config": {"workload": workload, "rows": n_all, "nnz": nnz_all, "max_row": max_row,
+                           "parallelism": "single GPU" if world == 1 else f"rows partitioned x{world} (RCB), P2P halo + mailbox all-reduce over NVLink",
                            "tolerance": "eps of dtype (Eigen default)" if args.tol < 0 else args.tol,
                            "pcg_iterations_last_step": its, "l2_policy": "inputs larger than L2 (matrix + vectors >> 126 MB)",
                            "setup_s": setup_s},
                 "e2e": {"value": total_steps / (e2e_ms_max / 1e3), "unit": "steps/s", "h2d_bytes_per_step": 4 * V, "d2h_bytes_per_step": 4 * V},
-                "gpu_launches": int(launches + st["kernel_launches"] * 0), "roofline": roof, "cpu_baseline": cpu, "clocks": clocks}
+                "gpu_launches": launches_all, "roofline": roof, "cpu_baseline": cpu, "clocks": clocks}
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

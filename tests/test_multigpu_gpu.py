@@ -163,3 +163,27 @@ def test_unconnected_partition_and_bicgstab_are_refused():
     G.set_equation(2)
     with pytest.raises(feab.FeabError):
         G.step(1)
+
+
+def test_one_process_per_gpu_partitioned_solve():
+    """Real ranks: torchrun with one process per visible GPU (2..8) runs tests/mp_partitioned.py -- cudaIpc peer
+    mappings, halo pushes and mailbox all-reduces over NVLink, WHILE-graph and host-batched loops, parity against the
+    fp64 oracle.  Skipped on a single-GPU box (the virtual-rank tests above cover the data path there)."""
+    import os
+    import socket
+    import subprocess
+    import sys
+    import torch
+    ngpu = torch.cuda.device_count()
+    if ngpu < 2:
+        pytest.skip("needs >= 2 GPUs")
+    world = min(ngpu, 8)
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr", "127.0.0.1",
+           "--master-port", str(port), os.path.join(root, "tests", "mp_partitioned.py")]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=900, cwd=root)
+    assert out.returncode == 0 and "MP_PARTITIONED_OK" in out.stdout, out.stdout[-3000:] + out.stderr[-3000:]
