@@ -9,7 +9,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libfeab.so")
 SOURCES = ["feab.cu"]
-HEADERS = ["common.cuh", "pattern.cuh", "assembly.cuh", "solver.cuh", "bicgstab.cuh", "spmv_tma.cuh", os.path.join("..", "..", "include", "feab.h")]
+HEADERS = ["common.cuh", "pattern.cuh", "assembly.cuh", "solver.cuh", "bicgstab.cuh", "spmv_tma.cuh", "comm.cuh", "partition.cuh",
+           os.path.join("..", "..", "include", "feab.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC", "-shared"]
 
 
@@ -36,6 +37,29 @@ def build(force: bool = False, verbose: bool = False) -> str:
     return LIB
 
 
+ROOT = os.path.dirname(HERE)
+CPP_DRIVER_SRC = os.path.join(ROOT, "tests", "cpp", "cuda_solver_driver.cpp")
+CPP_DRIVER = os.path.join(ROOT, "tests", "cpp", "cuda_solver_driver")
+
+
+def build_cpp_host(force: bool = False) -> str:
+    """g++ build of the headless C++ host program that drives include/FEM/CUDASolver.hpp (the C++ mirror of the
+    reference's Solver interface) against libfeab.so.  Host C++ only; links the C ABI, nothing else."""
+    inc = os.path.join(ROOT, "include")
+    deps = [CPP_DRIVER_SRC, LIB] + [os.path.join(inc, "FEM", f) for f in os.listdir(os.path.join(inc, "FEM"))] + \
+           [os.path.join(inc, "feab.h"), os.path.join(inc, "Utils", "Surface.hpp")]
+    if not force and os.path.exists(CPP_DRIVER) and all(os.path.getmtime(d) <= os.path.getmtime(CPP_DRIVER) for d in deps):
+        return CPP_DRIVER
+    cmd = [os.environ.get("CXX", "g++"), "-std=c++17", "-O2", "-Wall", "-I", inc, CPP_DRIVER_SRC, "-o", CPP_DRIVER, "-L", HERE, "-lfeab",
+           "-Wl,-rpath,$ORIGIN/../../fea_visualizer_b200"]
+    out = subprocess.run(cmd, capture_output=True, text=True)
+    if out.returncode != 0:
+        sys.stderr.write(out.stdout + out.stderr)
+        raise RuntimeError("g++ failed building tests/cpp/cuda_solver_driver")
+    return CPP_DRIVER
+
+
 if __name__ == "__main__":
     build(force="--force" in sys.argv, verbose=True)
     print(LIB)
+    print(build_cpp_host(force="--force" in sys.argv))
