@@ -181,7 +181,8 @@ def main():
     ap.add_argument("--cpu-nu", type=int, default=env_int("FEAB_BENCH_CPU_NU", 316))
     ap.add_argument("--cpu-steps", type=int, default=3)
     ap.add_argument("--no-cpu", action="store_true")
-    ap.add_argument("--loop", default="graph", choices=["graph", "host"], help="solve-loop driver: device-side WHILE graph or host-batched")
+    ap.add_argument("--loop", default=os.environ.get("FEAB_BENCH_LOOP", "auto"), choices=["auto", "persistent", "graph", "host"],
+                    help="solve-loop driver: auto = the library default; persistent whole-solve kernel, device-side WHILE graph, or host-batched")
     ap.add_argument("--tol", type=float, default=-1.0, help="<0: epsilon of the arithmetic type (Eigen default)")
     args = ap.parse_args()
 
@@ -235,8 +236,8 @@ def main():
         F.mg_config(rank, world)
     if args.tol >= 0:
         F.set_solver(tolerance=args.tol)
-    if args.loop == "host":
-        F.set_solver(loop_mode=feab.LOOP_HOST_BATCHED)
+    if args.loop != "auto":
+        F.set_solver(loop_mode={"host": feab.LOOP_HOST_BATCHED, "graph": feab.LOOP_GRAPH_WHILE, "persistent": feab.LOOP_PERSISTENT}[args.loop])
     t0 = time.perf_counter()
     F.set_mesh(xyz, tri, ob)
     if world > 1:
@@ -262,6 +263,7 @@ def main():
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
+    F.pcg_profile(reset=True)
     # --- device-resident timed region ---
     barrier()
     F.step(args.steps)                       # K steps in one call; CUDA events on the solver stream bracket it inside
@@ -270,6 +272,13 @@ def main():
     ms = st["last_call_ms"]
     its = st["iterations"]
     launches = st["kernel_launches"] - launches0
+    solve_ms = st.get("solve_ms", 0.0)       # persistent loop: device time of the last step's PCG kernel(s)
+    prof = F.pcg_profile(reset=True)          # FEAB_PCG_PROF=1: where CTA 0 of the persistent kernel spent its time
+    if prof["iterations"]:
+        prof = {"us_per_iteration": {k: v / prof["iterations"] / 1e3 for k, v in prof["ns"].items()}, "iterations": prof["iterations"]}
+        sys.stderr.write(f"[rank {rank}] pcg phase profile: {json.dumps(prof)}\n")
+    else:
+        prof = None
     # --- end-to-end through the reference-facing call with HOST buffers ---
     host = torch.empty(V, dtype=torch.float32).pin_memory()
     host.copy_(torch.from_numpy(F.get_values()))
@@ -310,6 +319,10 @@ def main():
                 "traffic_source": "profiles/r01_spmv_traffic.json (ncu --set full, per launch)", "peak_source": peak_src, "frac_of_nominal_8TBps": k0["GBps"] / 8000.0,
                 "pcg_iteration": {"ms": it_ms, "algorithmic_bytes": it_bytes, "GBps": it_bytes / it_ms / 1e6,
                                   "frac": it_bytes / it_ms / 1e6 / peak},
+                "pcg_persistent_last_step": None if not solve_ms else {
+                    "ms": solve_ms, "iterations": its, "algorithmic_bytes": (its[0] + its[1]) * it_bytes_row * n_all,
+                    "GBps": (its[0] + its[1]) * it_bytes_row * n_all / solve_ms / 1e6,
+                    "frac": (its[0] + its[1]) * it_bytes_row * n_all / solve_ms / 1e6 / peak},
                 "whole_step": {"algorithmic_bytes": step_bytes, "GBps": step_bytes / (ms_max / args.steps) / 1e6,
                                "frac": step_bytes / (ms_max / args.steps) / 1e6 / peak},
                 "kernels": kernels}
@@ -320,6 +333,8 @@ def main():
         roof = {"bound": "hbm", "kernel": "whole Gray-Scott step (rhs_init + PCG iterations), per GPU", "achieved": gbps, "peak": peak,
                 "unit": "GB/s", "frac": gbps / peak, "traffic": None, "algorithmic_bytes": step_bytes / world, "peak_source": peak_src,
                 "frac_of_nominal_8TBps": gbps / 8000.0,
+                "pcg_persistent_last_step": None if not solve_ms else {
+                    "ms": solve_ms, "iterations": its, "per_gpu_GBps": (its[0] + its[1]) * it_bytes_row * n_all / solve_ms / 1e6 / world},
                 "halo": {"ghost_columns_total": ghosts_all, "bytes_per_iteration_total": ghosts_all * rb,
                          "allreduces_per_iteration": 2, "collective": "P2P stores + mailbox flags over NVLink inside the solver kernels"}}
 
@@ -340,10 +355,10 @@ def main():
                 "config": {"workload": workload, "rows": n_all, "nnz": nnz_all, "max_row": max_row,
                            "parallelism": "single GPU" if world == 1 else f"rows partitioned x{world} (RCB), P2P halo + mailbox all-reduce over NVLink",
                            "tolerance": "eps of dtype (Eigen default)" if args.tol < 0 else args.tol,
-                           "pcg_iterations_last_step": its, "l2_policy": "inputs larger than L2 (matrix + vectors >> 126 MB)",
+                           "pcg_iterations_last_step": its, "loop": args.loop, "l2_policy": "inputs larger than L2 (matrix + vectors >> 126 MB)",
                            "setup_s": setup_s},
                 "e2e": {"value": total_steps / (e2e_ms_max / 1e3), "unit": "steps/s", "h2d_bytes_per_step": 4 * V, "d2h_bytes_per_step": 4 * V},
-                "gpu_launches": launches_all, "roofline": roof, "cpu_baseline": cpu, "clocks": clocks}
+                "gpu_launches": launches_all, "pcg_phase_profile": prof, "roofline": roof, "cpu_baseline": cpu, "clocks": clocks}
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

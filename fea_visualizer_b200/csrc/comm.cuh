@@ -21,10 +21,11 @@ namespace feab {
 constexpr int kMaxRanks = 8;
 constexpr unsigned long long kSpinTimeoutNs = 10ull * 1000 * 1000 * 1000;
 
+// One rank's contribution to one all-reduce, in "LL" form: every double travels as two 8-byte words, each carrying 32
+// data bits and the low 32 bits of the sequence number.  An 8-byte store is single-copy atomic, so a word whose flag
+// matches is complete by itself -- no fence between data and flag, one NVLink hop per all-reduce.
 struct ArSlot {
-    double v[4];
-    unsigned long long seq;
-    unsigned long long pad[3];
+    unsigned long long w[8];  // [2 k], [2 k + 1]: low / high half of value k, k < 4
 };
 struct CommCtrl {  // written by peers
     ArSlot slot[2][kMaxRanks];
@@ -56,6 +57,10 @@ struct HaloPlan {
     int dst_col[kMaxRanks] = {};        // first ghost column of my block on that neighbour
     const int* send_rows = nullptr;     // my local rows, ascending global unknown id per neighbour
     const int* send_nodes = nullptr;    // their mesh nodes
+    // inverse of the send lists, for pushes fused into the kernel that produces the values: for boundary row
+    // r >= n_int, push_tab[(r - n_int) * nnb + b] = ghost column on neighbour b that mirrors it, or -1
+    const int* push_tab = nullptr;
+    int n_int = 0;
     char* base[kMaxRanks] = {};         // neighbour arena base, indexed by RANK
     unsigned long long off_vec[5][kMaxRanks] = {};  // byte offsets of p[0], p[1], u, v, values in that arena, by RANK
 };
@@ -74,10 +79,26 @@ __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long
 __device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
     asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
-__device__ __forceinline__ double ld_volatile_f64(const double* p) {
-    double v;
-    asm volatile("ld.volatile.global.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
+__device__ __forceinline__ void st_relaxed_sys(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
     return v;
+}
+__device__ __forceinline__ void st_volatile_u64(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+// push_tab from the send lists (one thread per send entry; memset to -1 beforehand)
+__global__ void build_push_table(HaloPlan hp, int* __restrict__ tab) {
+    const int total = hp.send_off[hp.nnb];
+    for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < total; e += gridDim.x * blockDim.x) {
+        int b = 0;
+        while (e >= hp.send_off[b + 1]) b++;
+        tab[(size_t)(hp.send_rows[e] - hp.n_int) * hp.nnb + b] = hp.dst_col[b] + (e - hp.send_off[b]);
+    }
 }
 
 // Spin until *flag >= want (one thread).  Returns false on timeout.
@@ -92,6 +113,31 @@ __device__ __forceinline__ bool spin_until_ge(const unsigned long long* flag, un
         }
     }
     return true;
+}
+
+// LL mailbox: store value k of all-reduce `seq` into a (possibly remote) slot / wait for it in a local slot.
+__device__ __forceinline__ void ll_store(ArSlot* sl, int k, double v, unsigned long long seq) {
+    const unsigned long long bits = (unsigned long long)__double_as_longlong(v);
+    const unsigned long long flag = (seq & 0xffffffffull) << 32;
+    st_volatile_u64(&sl->w[2 * k], flag | (bits & 0xffffffffull));
+    st_volatile_u64(&sl->w[2 * k + 1], flag | (bits >> 32));
+}
+__device__ __forceinline__ double ll_wait(const ArSlot* sl, int k, unsigned long long seq, CommLocal* loc) {
+    const unsigned long long flag = seq & 0xffffffffull;
+    unsigned long long lo = ld_volatile_u64(&sl->w[2 * k]), hi = ld_volatile_u64(&sl->w[2 * k + 1]);
+    if ((lo >> 32) != flag || (hi >> 32) != flag) {
+        const unsigned long long t0 = globaltimer_ns();
+        while (true) {
+            lo = ld_volatile_u64(&sl->w[2 * k]);
+            hi = ld_volatile_u64(&sl->w[2 * k + 1]);
+            if ((lo >> 32) == flag && (hi >> 32) == flag) break;
+            if (globaltimer_ns() - t0 > kSpinTimeoutNs) {
+                loc->error = 1;
+                break;
+            }
+        }
+    }
+    return __longlong_as_double((long long)((hi << 32) | (lo & 0xffffffffull)));
 }
 
 // Fixed-order sum of per-CTA partials written earlier IN THIS KERNEL by other CTAs (L2 loads, never the
@@ -128,10 +174,8 @@ __device__ __forceinline__ void ar_publish(const Comm& cm, const R* part, int st
         for (int q = 0; q < cm.world; q++) {
             ArSlot* sl = &cm.ctrl[q]->slot[s & 1][cm.rank];
 #pragma unroll
-            for (int k = 0; k < K; k++) sl->v[k] = (double)tot[k];
+            for (int k = 0; k < K; k++) ll_store(sl, k, (double)tot[k], s);
         }
-        __threadfence_system();
-        for (int q = 0; q < cm.world; q++) st_release_sys(&cm.ctrl[q]->slot[s & 1][cm.rank].seq, s);
     }
 }
 
@@ -147,9 +191,8 @@ __device__ __forceinline__ void ar_consume(const Comm& cm, R (&out)[K]) {
         for (int k = 0; k < K; k++) acc[k] = (R)0;
         for (int q = 0; q < cm.world; q++) {
             const ArSlot* sl = &me->slot[s & 1][q];
-            spin_until_ge(&sl->seq, s, cm.loc);
 #pragma unroll
-            for (int k = 0; k < K; k++) acc[k] += (R)ld_volatile_f64(&sl->v[k]);
+            for (int k = 0; k < K; k++) acc[k] += (R)ll_wait(sl, k, s, cm.loc);
         }
 #pragma unroll
         for (int k = 0; k < K; k++) s_v[k] = (double)acc[k];

@@ -18,6 +18,7 @@
 #include "common.cuh"
 #include "partition.cuh"
 #include "pattern.cuh"
+#include "pcg_persistent.cuh"
 #include "solver.cuh"
 #include "spmv_tma.cuh"
 
@@ -97,6 +98,7 @@ struct SolverBase {
     virtual void get_state(int which, void* out) = 0;
     virtual void set_state(int which, const void* in) = 0;
     virtual void time_kernel(int kernel, int reps, double* ms, double* bytes) = 0;
+    virtual void pcg_profile(double* out16, int reset) = 0;
     virtual void mg_config(int rank, int world) = 0;
     virtual void mg_set_partition(const int32_t* part, int64_t V) = 0;
     virtual void mg_export(FeabMgExport* out) = 0;
@@ -158,7 +160,30 @@ class SolverT final : public SolverBase {
         if (const char* v = getenv("FEAB_SPMV")) spmv_variant_ = atoi(v);
         if (const char* v = getenv("FEAB_PREFETCH_X")) prefetch_x_ = atoi(v);
         setup_spmv_variants();
+        // persistent whole-solve kernel (pcg_persistent.cuh): same tile geometry as SpMV variant 4
+        using PCfg = TmaCfg<R, kPcgRows, kPcgCpr, kPcgStages>;
+        CK(cudaFuncSetAttribute(pcg_persistent<R, kPcgRows, kPcgCpr, kPcgStages, kPcgMinB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)PCfg::kSmemBytes));
+        int occ = 0;
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, pcg_persistent<R, kPcgRows, kPcgCpr, kPcgStages, kPcgMinB>, kPcgRows,
+                                                         PCfg::kSmemBytes));
+        int coop = 0;
+        CK(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device_));
+        pcg_max_grid_ = coop ? occ * sms_ : 0;
+        if (const char* v = getenv("FEAB_PCG_CTAS_PER_SM")) pcg_max_grid_ = std::min(pcg_max_grid_, std::max(1, atoi(v)) * sms_);
+        CK(cudaMalloc(&d_bar_, 4 * sizeof(unsigned long long)));
+        CK(cudaMemset(d_bar_, 0, 4 * sizeof(unsigned long long)));
+        for (int i = 0; i < 4; i++) CK(cudaEventCreate(&ev_solve_[i]));
+        if (getenv("FEAB_PCG_PROF")) {
+            CK(cudaMalloc(&d_prof_, 16 * sizeof(unsigned long long)));
+            CK(cudaMemset(d_prof_, 0, 16 * sizeof(unsigned long long)));
+        }
+        if (pcg_max_grid_ > 0) {
+            opt_.loop_mode = FEAB_LOOP_PERSISTENT;
+            d_ppart_.alloc((size_t)3 * pcg_max_grid_);
+        }
     }
+    static constexpr int kPcgRows = 512, kPcgCpr = 8, kPcgStages = 2, kPcgMinB = 2;
 
     // ---- SpMV variants: 0 = LDG/CSR-stream (solver.cuh), 1.. = TMA pipelines (spmv_tma.cuh) ----
     template <int ROWS, int CPR, int STAGES, int MINB>
@@ -218,6 +243,10 @@ class SolverT final : public SolverBase {
         if (d_st_) cudaFree(d_st_);
         if (d_bst_) cudaFree(d_bst_);
         if (d_loc_) cudaFree(d_loc_);
+        if (d_bar_) cudaFree(d_bar_);
+        if (d_prof_) cudaFree(d_prof_);
+        for (int i = 0; i < 4; i++)
+            if (ev_solve_[i]) cudaEventDestroy(ev_solve_[i]);
         close_peers();
         if (h_flag_) cudaFreeHost(h_flag_);
         cudaEventDestroy(ev0_);
@@ -367,6 +396,14 @@ class SolverT final : public SolverBase {
         }
         hp_.send_rows = d_send_rows_.p;
         hp_.send_nodes = d_send_nodes_.p;
+        hp_.n_int = (int)n_int_;
+        {
+            const size_t cells = (size_t)std::max<int64_t>((n_ - n_int_) * std::max(hp_.nnb, 1), 1);
+            d_push_tab_.alloc(cells);
+            CK(cudaMemsetAsync(d_push_tab_.p, 0xff, cells * sizeof(int), stream_));
+            if (total_send > 0) build_push_table<<<std::max(1, cdiv64(total_send, kBlock)), kBlock, 0, stream_>>>(hp_, d_push_tab_.p);
+            hp_.push_tab = d_push_tab_.p;
+        }
         // per-node maps and their inverses
         d_rowmap_.alloc(V);
         d_colmap_.alloc(V);
@@ -618,7 +655,8 @@ class SolverT final : public SolverBase {
     void set_options(const FeabSolverOptions* o) override {
         REQUIRE(o, FEAB_EINVAL, "set_solver_options: null");
         REQUIRE(o->solver == 0 || o->solver == 1, FEAB_EINVAL, "set_solver_options: solver");
-        REQUIRE(o->loop_mode == 0 || o->loop_mode == 1, FEAB_EINVAL, "set_solver_options: loop_mode");
+        REQUIRE(o->loop_mode >= 0 && o->loop_mode <= 2, FEAB_EINVAL, "set_solver_options: loop_mode");
+        REQUIRE(o->loop_mode != FEAB_LOOP_PERSISTENT || pcg_max_grid_ > 0, FEAB_EINVAL, "set_solver_options: device cannot launch cooperative kernels");
         REQUIRE(o->assembly == 0 || o->assembly == 1, FEAB_EINVAL, "set_solver_options: assembly");
         bool reassemble = o->assembly != opt_.assembly;
         opt_ = *o;
@@ -819,6 +857,38 @@ class SolverT final : public SolverBase {
     // PCG solve of slot `slot` into x.  capturing: build WHILE node into the graph being captured on stream_.
     void enqueue_pcg(int slot, const R* A, const R* dinv, R* x, bool capturing) {
         CgState<R>* st = d_st_ + slot;
+        if (!capturing && opt_.loop_mode == FEAB_LOOP_PERSISTENT) {
+            // the whole solve is one cooperative launch: no WHILE node, no host polling (pcg_persistent.cuh)
+            cudaGraphConditionalHandle none = 0;
+            ph_cg_begin(stream_, slot, x, none, 0);
+            CK(cudaMemsetAsync(d_bar_ + 2 * slot, 0, 2 * sizeof(unsigned long long), stream_));
+            PcgArgs<R> pa;
+            pa.rowptr = d_rowptr_.p;
+            pa.col = d_col_.p;
+            pa.A = A;
+            pa.dinv = dinv;
+            pa.x = x;
+            pa.r = d_r_[slot].p;
+            pa.p = d_p_[slot].p;
+            pa.y = d_y_.p;
+            pa.n = n_;
+            pa.num_tiles = std::max(1, cdiv64(n_, kPcgRows));
+            pa.first_halo_tile = first_halo_tile(kPcgRows);
+            pa.st = st;
+            pa.part = d_ppart_.p;
+            pa.bar = d_bar_ + 2 * slot;
+            pa.vec_p = slot == 0 ? kVecP0 : kVecP1;
+            pa.prof = d_prof_;
+            const int grid = std::min(pcg_max_grid_, pa.num_tiles);
+            using PCfg = TmaCfg<R, kPcgRows, kPcgCpr, kPcgStages>;
+            void* kargs[] = {(void*)&pa, (void*)&cm_, (void*)&hp_};
+            if (time_solves_) CK(cudaEventRecord(ev_solve_[2 * slot], stream_));
+            CK(cudaLaunchCooperativeKernel((const void*)pcg_persistent<R, kPcgRows, kPcgCpr, kPcgStages, kPcgMinB>, dim3(grid), dim3(kPcgRows), kargs,
+                                           PCfg::kSmemBytes, stream_));
+            if (time_solves_) CK(cudaEventRecord(ev_solve_[2 * slot + 1], stream_));
+            launches_ += 2;
+            return;
+        }
         if (capturing) {
             cudaStreamCaptureStatus status;
             cudaGraph_t graph;
@@ -936,9 +1006,12 @@ class SolverT final : public SolverBase {
         if (n_ > 0 && nsteps > 0) {
             ensure_operator();
             ph_push_state(stream_);
-            const bool graph_mode = opt_.loop_mode == FEAB_LOOP_GRAPH_WHILE;
+            // BiCGSTAB has no persistent kernel: it keeps the WHILE graph unless host batching was asked for
+            const bool graph_mode = opt_.loop_mode == FEAB_LOOP_GRAPH_WHILE || (opt_.loop_mode == FEAB_LOOP_PERSISTENT && use_bicgstab());
+            graph_mode_last_ = graph_mode;
             if (graph_mode && (!graph_exec_ || graph_eq_ != eq_)) build_graph();
             for (int s = 0; s < nsteps; s++) {
+                time_solves_ = !graph_mode && opt_.loop_mode == FEAB_LOOP_PERSISTENT && s == nsteps - 1;
                 if (graph_mode) {
                     CK(cudaGraphLaunch(graph_exec_, stream_));
                     graph_steps_++;
@@ -957,7 +1030,17 @@ class SolverT final : public SolverBase {
         CK(cudaEventElapsedTime(&ms, ev0_, ev1_));
         last_ms_ = ms;
         last_steps_ = nsteps;
-        if (n_ > 0 && nsteps > 0 && opt_.loop_mode == FEAB_LOOP_GRAPH_WHILE) account_graph_launches(nsteps);
+        if (n_ > 0 && nsteps > 0 && graph_mode_last_) account_graph_launches(nsteps);
+        solve_ms_ = 0;
+        if (time_solves_) {  // device time of the last step's persistent PCG kernels
+            const int ns = eq_ == FEAB_EQ_REACTION_DIFFUSION ? 2 : 1;
+            for (int sl = 0; sl < ns; sl++) {
+                float t = 0;
+                if (cudaEventElapsedTime(&t, ev_solve_[2 * sl], ev_solve_[2 * sl + 1]) == cudaSuccess) solve_ms_ += t;
+            }
+            cudaGetLastError();
+            time_solves_ = false;
+        }
         check_comm_error();
     }
 
@@ -1003,6 +1086,7 @@ class SolverT final : public SolverBase {
         s->last_call_ms = last_ms_;
         s->last_call_steps = last_steps_;
         s->kernel_launches = launches_;
+        s->solve_ms = solve_ms_;
     }
 
     // ---------------------------------------------------------------- measurement hook
@@ -1088,6 +1172,16 @@ class SolverT final : public SolverBase {
         *bytes_out = bytes;
         // leave a clean state behind
         CK(cudaMemset(d_st_, 0, 2 * sizeof(CgState<R>)));
+    }
+
+    void pcg_profile(double* out16, int reset) override {
+        for (int i = 0; i < 16; i++) out16[i] = 0;
+        if (!d_prof_) return;
+        CK(cudaSetDevice(device_));
+        unsigned long long h[16];
+        CK(cudaMemcpy(h, d_prof_, sizeof(h), cudaMemcpyDeviceToHost));
+        for (int i = 0; i < 16; i++) out16[i] = (double)h[i];
+        if (reset) CK(cudaMemset(d_prof_, 0, sizeof(h)));
     }
 
     // ---------------------------------------------------------------- partitioned solve: configuration
@@ -1259,7 +1353,7 @@ class SolverT final : public SolverBase {
     int rank_ = 0, world_ = 1;
     std::vector<int> h_part_;          // part of every mesh vertex (all ranks hold the same array)
     bool part_given_ = false;
-    DevBuf<int> d_part_of_, d_rowmap_, d_colmap_, d_node_of_col_, d_glob_of_col_, d_send_rows_, d_send_nodes_;
+    DevBuf<int> d_part_of_, d_rowmap_, d_colmap_, d_node_of_col_, d_glob_of_col_, d_send_rows_, d_send_nodes_, d_push_tab_;
     const int* rowmap_p_ = nullptr;      // per node: local row or -1
     const int* colmap_p_ = nullptr;      // per node: local column (row or ghost) or -1
     const int* node_of_col_p_ = nullptr; // per local column: mesh node
@@ -1288,6 +1382,15 @@ class SolverT final : public SolverBase {
     cudaGraphExec_t graph_exec_ = nullptr;
     int graph_eq_ = -1;
     int64_t graph_steps_ = 0;
+
+    // persistent whole-solve kernel
+    int pcg_max_grid_ = 0;
+    unsigned long long* d_bar_ = nullptr;
+    unsigned long long* d_prof_ = nullptr;  // FEAB_PCG_PROF=1: phase timers of the persistent kernel (CTA 0)
+    DevBuf<R> d_ppart_;
+    cudaEvent_t ev_solve_[4] = {};
+    bool time_solves_ = false, graph_mode_last_ = false;
+    double solve_ms_ = 0;
 
     double last_ms_ = 0;
     int64_t last_steps_ = 0;
@@ -1482,6 +1585,10 @@ int feab_set_state(FeabHandle* h, int which, const void* in) { FEAB_TRY(h, h->im
 int feab_time_kernel(FeabHandle* h, int kernel, int reps, double* ms, double* bytes) {
     if (!ms || !bytes) return FEAB_EINVAL;
     FEAB_TRY(h, h->impl->time_kernel(kernel, reps, ms, bytes));
+}
+int feab_pcg_profile(FeabHandle* h, double* out16, int reset) {
+    if (!out16) return FEAB_EINVAL;
+    FEAB_TRY(h, h->impl->pcg_profile(out16, reset));
 }
 int feab_mg_config(FeabHandle* h, int rank, int world) { FEAB_TRY(h, h->impl->mg_config(rank, world)); }
 int feab_mg_set_partition(FeabHandle* h, const int32_t* part, int64_t V) { FEAB_TRY(h, h->impl->mg_set_partition(part, V)); }

@@ -18,7 +18,7 @@ BC_DIRICHLET, BC_NEUMANN = 0, 1
 MAT_MASS, MAT_STIFFNESS, MAT_ADVECTION = 0, 1, 2
 SOLVER_PARITY_CG, SOLVER_BICGSTAB = 0, 1
 ASSEMBLY_SCATTER, ASSEMBLY_ORDERED = 0, 1
-LOOP_GRAPH_WHILE, LOOP_HOST_BATCHED = 0, 1
+LOOP_GRAPH_WHILE, LOOP_HOST_BATCHED, LOOP_PERSISTENT = 0, 1, 2
 
 # every symbol include/feab.h declares (checked by tests/test_abi.py without a GPU)
 ABI_SYMBOLS = [
@@ -27,7 +27,7 @@ ABI_SYMBOLS = [
     "feab_set_solver_options", "feab_get_solver_options", "feab_clear", "feab_set_values", "feab_get_values", "feab_brush",
     "feab_step", "feab_unstable", "feab_last_stats", "feab_get_state", "feab_set_state", "feab_time_kernel",
     "feab_device_info", "feab_mg_config", "feab_mg_set_partition", "feab_partition_rcb", "feab_mg_export", "feab_mg_connect",
-    "feab_mg_get_layout", "feab_mg_get_maps", "feab_mg_group_step",
+    "feab_mg_get_layout", "feab_mg_get_maps", "feab_mg_group_step", "feab_pcg_profile",
 ]
 
 
@@ -210,7 +210,7 @@ class Feab:
         s = FeabStats()
         self._ck(self.lib.feab_last_stats(self.h, C.byref(s)))
         return {"iterations": list(s.iterations), "rel_residual": list(s.rel_residual), "last_call_ms": s.last_call_ms,
-                "last_call_steps": s.last_call_steps, "kernel_launches": s.kernel_launches}
+                "last_call_steps": s.last_call_steps, "kernel_launches": s.kernel_launches, "solve_ms": s.solve_ms}
 
     def get_state(self, which):
         out = np.empty(max(self.num_unknowns(), 1), dtype=self.real)
@@ -226,6 +226,12 @@ class Feab:
         ms, by = C.c_double(), C.c_double()
         self._ck(self.lib.feab_time_kernel(self.h, C.c_int(kernel), C.c_int(reps), C.byref(ms), C.byref(by)))
         return ms.value, by.value
+
+    def pcg_profile(self, reset=True):
+        out = (C.c_double * 16)()
+        self._ck(self.lib.feab_pcg_profile(self.h, out, C.c_int(1 if reset else 0)))
+        names = ["spmv", "bar1", "ar1", "update", "bar2", "ar2", "direction", "bar3", "push"]
+        return {"ns": dict(zip(names, list(out)[:9])), "iterations": int(out[9])}
 
     def device_info(self):
         sm, mem = C.c_int(), C.c_int64()

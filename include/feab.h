@@ -40,9 +40,12 @@ enum { FEAB_SOLVER_PARITY_CG = 0, FEAB_SOLVER_BICGSTAB = 1 };
  * incident triangles in ascending element order -- Eigen's setFromTriplets order
  * (lib/eigen/Eigen/src/SparseCore/SparseMatrix.h:1475-1511), deterministic. */
 enum { FEAB_ASSEMBLY_SCATTER = 0, FEAB_ASSEMBLY_ORDERED = 1 };
-/* Solve-loop driver: one CUDA graph per step with a device-side WHILE node (no host round trips), or
- * host-batched iterations with a flag poll per batch. */
-enum { FEAB_LOOP_GRAPH_WHILE = 0, FEAB_LOOP_HOST_BATCHED = 1 };
+/* Solve-loop driver.  PERSISTENT (default): the whole PCG solve is ONE cooperative kernel that stays resident and
+ * separates the phases of an iteration by grid barriers (no launches, no host round trips inside a solve).
+ * GRAPH_WHILE: one CUDA graph per step with a device-side WHILE node around three kernels per iteration.
+ * HOST_BATCHED: the same three kernels launched in batches with a flag poll per batch.  BiCGSTAB uses GRAPH_WHILE
+ * when PERSISTENT is selected. */
+enum { FEAB_LOOP_GRAPH_WHILE = 0, FEAB_LOOP_HOST_BATCHED = 1, FEAB_LOOP_PERSISTENT = 2 };
 
 enum {
     FEAB_OK = 0,
@@ -77,7 +80,7 @@ typedef struct {
     double last_call_ms;       /* device time of the last feab_step call (CUDA events on the solver stream) */
     int64_t last_call_steps;
     int64_t kernel_launches;   /* kernels launched by this handle since creation (graph nodes counted per execution) */
-    double solve_ms;           /* device time inside the PCG loops of the last call when timing detail is on, else 0 */
+    double solve_ms;           /* PERSISTENT loop: device time of the PCG kernel(s) of the LAST step of the last call; else 0 */
 } FeabStats;
 
 /* -- lifetime ------------------------------------------------------------------------------- */
@@ -180,6 +183,10 @@ int feab_mg_group_step(FeabHandle** handles, int count, int nsteps);
  * launch (CUDA events on the solver stream) and the algorithmic bytes one launch moves.
  * kernel: 0 = SpMV+dot, 1 = PCG vector update, 2 = PCG direction update, 3 = RHS build for the current equation */
 int feab_time_kernel(FeabHandle* h, int kernel, int reps, double* ms_per_launch, double* algorithmic_bytes);
+/* With FEAB_PCG_PROF=1 in the environment at feab_create: nanoseconds CTA 0 of the persistent PCG kernel spent in
+ * [0] SpMV phase, [1] barrier + partial sums, [2] all-reduce of p.Ap, [3] update phase, [4] barrier + sums, [5] all-reduce
+ * of |r|^2, r.z, [6] direction phase, [7] barrier, [8] halo push; [9] = iterations counted.  Zeros when profiling is off. */
+int feab_pcg_profile(FeabHandle* h, double* out16, int reset);
 int feab_device_info(const FeabHandle* h, int* sm_count, int64_t* total_mem_bytes, char* name64);
 
 #ifdef __cplusplus
