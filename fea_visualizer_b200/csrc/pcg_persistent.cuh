@@ -398,9 +398,9 @@ __global__ void __launch_bounds__(ROWS, MINB) pcg_persistent(PcgArgs<R> a, Comm 
             // and a relaxed flag store is enough (a release here would cost another system fence on the critical path).  Every CTA counts the push so that its next halo wait
             // asks for the right flag value.
             halo_seq += 1;
-            if (blockIdx.x == 0 && threadIdx.x == 0) {
-                cm.loc->halo_seq = halo_seq;
-                for (int b = 0; b < hp.nnb; b++) st_relaxed_sys(&cm.ctrl[hp.nb_rank[b]]->halo_flag[cm.rank], halo_seq);
+            if (blockIdx.x == 0) {  // one thread per neighbour: the flag stores leave in parallel
+                if (threadIdx.x == 0) cm.loc->halo_seq = halo_seq;
+                if ((int)threadIdx.x < hp.nnb) st_relaxed_sys(&cm.ctrl[hp.nb_rank[threadIdx.x]]->halo_flag[cm.rank], halo_seq);
             }
         }
         PCG_STAMP(8)
