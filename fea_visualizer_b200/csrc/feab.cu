@@ -2,6 +2,7 @@
 // assembly.cuh and solver.cuh.  One handle = one mesh on one GPU; everything stays resident in HBM.
 // There is no CPU fallback: without a CUDA device feab_create fails with FEAB_ENOGPU.
 #include "../../include/feab.h"
+#include "../../include/feab_surface.h"
 
 #include <unistd.h>
 
@@ -91,6 +92,7 @@ struct SolverBase {
     virtual void clear() = 0;
     virtual void set_values(const float* v) = 0;
     virtual void get_values(float* v) = 0;
+    virtual const float* values_device() = 0;
     virtual void brush(const int64_t* nodes, int64_t count, float strength) = 0;
     virtual void step(float* values, int nsteps, int sync) = 0;
     virtual int unstable() = 0;
@@ -679,6 +681,12 @@ class SolverT final : public SolverBase {
         CK(cudaSetDevice(device_));
         CK(cudaMemcpyAsync(d_values_.p, v, V_ * sizeof(float), cudaMemcpyHostToDevice, stream_));
         CK(cudaStreamSynchronize(stream_));
+    }
+    const float* values_device() override {
+        REQUIRE(have_mesh_, FEAB_ENOMESH, "values_device: no mesh");
+        CK(cudaSetDevice(device_));
+        CK(cudaStreamSynchronize(stream_));
+        return d_values_.p;
     }
     void get_values(float* v) override {
         REQUIRE(have_mesh_ && v, FEAB_ENOMESH, "get_values: no mesh");
@@ -1570,6 +1578,10 @@ int feab_get_solver_options(const FeabHandle* h, FeabSolverOptions* o) {
 int feab_clear(FeabHandle* h) { FEAB_TRY(h, h->impl->clear()); }
 int feab_set_values(FeabHandle* h, const float* v) { FEAB_TRY(h, h->impl->set_values(v)); }
 int feab_get_values(FeabHandle* h, float* v) { FEAB_TRY(h, h->impl->get_values(v)); }
+int feab_values_device(FeabHandle* h, const float** out) {
+    if (!out) return FEAB_EINVAL;
+    FEAB_TRY(h, *out = h->impl->values_device());
+}
 int feab_brush(FeabHandle* h, const int64_t* nodes, int64_t count, float strength) { FEAB_TRY(h, h->impl->brush(nodes, count, strength)); }
 int feab_step(FeabHandle* h, float* values, int nsteps, int sync) { FEAB_TRY(h, h->impl->step(values, nsteps, sync)); }
 int feab_unstable(FeabHandle* h, int* out) {
