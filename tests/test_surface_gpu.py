@@ -1,0 +1,208 @@
+"""GPU parity tests of the Surface-side rows, through the C ABI of include/feab_surface.h.
+
+Bars: .ply files BYTE-IDENTICAL to the ones the unmodified reference writes (golden fixtures + the compiled reference
+on larger meshes); boundary flags, colour map, OBJ ingest bit-exact; smooth normals within 1e-5 relative of the
+sequential restatement (the shader's float atomics leave the summation order open -- parity of that kernel is unpinned).
+"""
+import os
+
+import numpy as np
+import pytest
+
+from fea_visualizer_b200 import feab, meshes
+from fea_visualizer_b200.surface import MESH_CLOSED, MESH_MIRRORED, MESH_OPEN, DeviceSurface
+from oracle import surface_oracle as S
+from tests.golden.make_golden_surface import write_obj
+from tests.util import load_golden
+
+pytestmark = pytest.mark.gpu
+CASES = [(0.25, 0.0), (0.25, 0.1), (0.0, 0.3), (-0.5, 0.05), (1.5, -0.2)]
+needs_ref = pytest.mark.skipif(not S.available(), reason="oracle/_ref/libfea_surface_ref.so not built")
+
+
+def bits(a):
+    return np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
+
+
+# ------------------------------------------------------------------------------------------------- N1: .ply exporter
+@pytest.mark.parametrize("name", ["ico6d", "grid", "disk"])
+@pytest.mark.parametrize("mt", [MESH_OPEN, MESH_CLOSED, MESH_MIRRORED])
+def test_ply_bytes_equal_golden(name, mt, tmp_path):
+    g = load_golden("ref_surface.npz")
+    D = DeviceSurface()
+    D.set_mesh(g[f"{name}_xyz"], g[f"{name}_nrm"], g[f"{name}_tri"])
+    D.set_values(g[f"{name}_val"])
+    for k, (ve, thr) in enumerate(CASES):
+        p = str(tmp_path / "o.ply")
+        D.export_to_ply(p, ve, thr, mt)
+        assert open(p, "rb").read() == g[f"ply_{name}_{mt}_{k}"].tobytes(), (name, mt, k)
+
+
+@needs_ref
+@pytest.mark.parametrize("mt", [MESH_OPEN, MESH_CLOSED, MESH_MIRRORED])
+def test_ply_bytes_equal_compiled_reference_100k(mt, tmp_path):
+    xyz, tri = meshes.icosphere(100, displace=True)          # 100 002 vertices, 200 000 triangles
+    nrm = (xyz / np.linalg.norm(xyz, axis=1, keepdims=True)).astype(np.float32)
+    val = (np.sin(7 * xyz[:, 0]) * np.cos(5 * xyz[:, 1]) + 0.3 * np.sin(9 * xyz[:, 2])).astype(np.float32)
+    R = S.RefSurface()
+    R.set_mesh(xyz, nrm, tri)
+    R.set_values(val)
+    D = DeviceSurface()
+    D.set_mesh(xyz, nrm, tri)
+    D.set_values(val)
+    for ve, thr in [(0.25, 0.2), (0.1, -5.0)]:       # a clipped field, and everything above the threshold
+        pr, pd = str(tmp_path / "r.ply"), str(tmp_path / "d.ply")
+        R.export_to_ply(pr, ve, thr, mt)
+        D.export_to_ply(pd, ve, thr, mt)
+        assert open(pr, "rb").read() == open(pd, "rb").read()
+
+
+def test_ply_everything_below_threshold_is_empty(tmp_path):
+    xyz, tri = meshes.icosphere(4)
+    D = DeviceSurface()
+    D.set_mesh(xyz, xyz, tri)
+    nv, nt = D.ply_build(0.25, 0.5, MESH_OPEN, fetch=False)       # values are all 0 < 0.5
+    assert (nv, nt) == (0, 0)
+    p = str(tmp_path / "e.ply")
+    D.export_to_ply(p, 0.25, 0.5, MESH_CLOSED)
+    assert b"element vertex 0\n" in open(p, "rb").read() and b"element face 0\n" in open(p, "rb").read()
+
+
+def test_ply_open_above_threshold_keeps_the_mesh():
+    # size-independent property: with every value above the threshold an Open export is the extruded mesh itself --
+    # one output vertex per referenced input vertex in first-use order, one output triangle per input triangle
+    xyz, tri = meshes.icosphere(300)                               # 900 002 vertices
+    nrm = xyz.copy()
+    val = (0.5 + 0.25 * np.sin(3 * xyz[:, 0])).astype(np.float32)
+    D = DeviceSurface()
+    D.set_mesh(xyz, nrm, tri)
+    D.set_values(val)
+    pos, v, col, otri = D.ply_build(0.25, 0.0, MESH_OPEN)
+    assert len(pos) == len(xyz) and len(otri) == len(tri)
+    flat = tri.reshape(-1).astype(np.int64)
+    _, first = np.unique(flat, return_index=True)
+    order = flat[np.sort(first)]                                    # input vertices in order of first use
+    assert (bits(v) == bits(val[order])).all()
+    s = (val * np.float32(0.25)).astype(np.float32)
+    ext = ((s[:, None] * nrm).astype(np.float32) + xyz).astype(np.float32)
+    assert (bits(pos) == bits(ext[order])).all()
+    inv = np.empty(len(xyz), np.int64)
+    inv[order] = np.arange(len(xyz))
+    assert (otri.astype(np.int64) == inv[tri.astype(np.int64)]).all()
+    assert (bits(col) == bits(D.get_color(v))).all()
+
+
+def test_ply_closed_doubles_the_surface():
+    xyz, tri = meshes.icosphere(20)
+    val = np.full(len(xyz), 0.5, np.float32)
+    D = DeviceSurface()
+    D.set_mesh(xyz, xyz, tri)
+    D.set_values(val)
+    pos, v, col, otri = D.ply_build(0.25, 0.1, MESH_CLOSED)
+    assert len(otri) == 2 * len(tri) and len(pos) == 2 * len(xyz)
+    # the projected copy carries the threshold as its value (Surface.cpp:264)
+    assert np.isclose(np.sort(v)[: len(xyz)], 0.1).all() and np.isclose(np.sort(v)[len(xyz):], 0.5).all()
+
+
+def test_values_hand_over_from_the_solver_is_zero_copy_equal():
+    xyz, tri = meshes.icosphere(16)
+    ob = meshes.boundary_flags(len(xyz), tri)
+    F = feab.Feab(real=64)
+    F.set_mesh(xyz, tri, ob)
+    F.set_equation(0)
+    v0 = np.zeros(len(xyz), np.float32)
+    v0[meshes.seed_nodes(len(xyz))] = 1.0
+    F.set_values(v0)
+    F.step(3)
+    A, B = DeviceSurface(), DeviceSurface()
+    for X in (A, B):
+        X.set_mesh(xyz, xyz, tri)
+    A.set_values(F.get_values())
+    B.set_values_from_solver(F)
+    ra, rb = A.ply_build(0.25, 0.01, MESH_MIRRORED), B.ply_build(0.25, 0.01, MESH_MIRRORED)
+    assert len(ra[0]) > 0
+    for x, y in zip(ra, rb):
+        assert (x.view(np.uint32) == y.view(np.uint32)).all()
+
+
+# ------------------------------------------------------------------------------------------------- colour map
+def test_color_map_bit_exact():
+    g = load_golden("ref_surface.npz")
+    D = DeviceSurface()
+    for cm, coeffs in S.COLOR_MAPS.items():
+        D.set_color_map(coeffs)
+        assert (bits(D.get_color(g[f"cm_{cm}_t"])) == bits(g[f"cm_{cm}_rgb"])).all(), cm
+
+
+# ------------------------------------------------------------------------------------------------- N2: ingest
+@pytest.mark.parametrize("name", ["ico6d", "grid", "disk"])
+def test_boundary_detection_equals_reference(name):
+    g = load_golden("ref_surface.npz")
+    D = DeviceSurface()
+    D.set_mesh(g[f"{name}_xyz"], None, g[f"{name}_tri"])
+    ob, nb, closed = D.detect_boundary()
+    assert (ob == g[f"{name}_onb"]).all() and nb == int(g[f"{name}_onb"].sum()) and closed == (nb == 0)
+
+
+def test_boundary_detection_odd_cases():
+    # edge shared by 3 triangles (count 3: not a boundary edge), a degenerate triangle (edge a-a counts 2), an isolated vertex
+    xyz = np.zeros((7, 3), np.float32)
+    tri = np.array([[0, 1, 2], [1, 0, 3], [0, 1, 4], [5, 5, 6]], np.uint32)
+    D = DeviceSurface()
+    D.set_mesh(xyz, None, tri)
+    ob, nb, closed = D.detect_boundary()
+    assert (ob == meshes.boundary_flags(7, tri)).all()
+    # edge 0-1 is used three times; every other edge of the first three triangles once -> 0..4 flagged via those;
+    # triangle (5,5,6): edge 5-5 counts twice, edges 5-6 and 6-5 are the same pair used twice -> nothing flagged
+    assert ob.tolist() == [1, 1, 1, 1, 1, 0, 0] and nb == 5 and not closed
+
+
+def test_boundary_detection_large_mesh_properties():
+    xyz, tri = meshes.icosphere(500)                                  # closed: no boundary
+    D = DeviceSurface()
+    D.set_mesh(xyz, None, tri)
+    ob, nb, closed = D.detect_boundary()
+    assert nb == 0 and closed and not ob.any()
+    xyz, tri = meshes.grid(1500, 1000)                                # open: the rim
+    D.set_mesh(xyz, None, tri)
+    ob, nb, closed = D.detect_boundary()
+    assert nb == 2 * (1500 + 1000) and not closed
+    assert (ob == meshes.boundary_flags(len(xyz), tri)).all()
+
+
+def test_obj_ingest_equals_reference(tmp_path):
+    g = load_golden("ref_surface.npz")
+    for name in ("ico6d", "disk"):
+        p = str(tmp_path / (name + ".obj"))
+        write_obj(p, g[f"{name}_xyz"], g[f"{name}_nrm"], g[f"{name}_tri"])
+        D = DeviceSurface()
+        D.init_from_obj(p)
+        xyz, nrm, tri, ob = D.get_mesh()
+        assert (bits(xyz) == bits(g[f"{name}_xyz"])).all() and (tri == g[f"{name}_tri"]).all()
+        assert (bits(nrm) == bits(g[f"{name}_objnrm"])).all()
+        assert (ob == g[f"{name}_onb"]).all() and D.counts()[2] == int(ob.sum())
+
+
+def test_obj_without_normals_is_rejected(tmp_path):
+    p = str(tmp_path / "n.obj")
+    open(p, "w").write("v 0 0 0\nv 1 0 0\nv 0 1 0\nf 1 2 3\n")
+    D = DeviceSurface()
+    with pytest.raises(feab.FeabError, match="does not contain normals"):
+        D.init_from_obj(p)
+    with pytest.raises(feab.FeabError, match="valid file"):
+        D.init_from_obj(str(tmp_path / "missing.obj"))
+
+
+# ------------------------------------------------------------------------------------------------- N3: normals
+@pytest.mark.parametrize("ve", [0.0, 0.25, 3.0])
+def test_smooth_normals_vs_restatement(ve):
+    xyz, tri = meshes.icosphere(24, displace=True)
+    nrm = (xyz / np.linalg.norm(xyz, axis=1, keepdims=True)).astype(np.float32)
+    val = (np.sin(4 * xyz[:, 0]) + 0.5 * xyz[:, 1]).astype(np.float32)
+    D = DeviceSurface()
+    D.set_mesh(xyz, nrm, tri)
+    D.set_values(val)
+    got = D.calculate_normals(ve)
+    want = S.smooth_normals(xyz, nrm, val, tri, ve)
+    scale = np.abs(want).max()
+    assert np.abs(got - want).max() <= 1e-5 * scale     # summation order only
