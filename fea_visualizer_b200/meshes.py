@@ -114,7 +114,9 @@ def boundary_flags(num_vertices: int, tri: np.ndarray) -> np.ndarray:
     e = np.concatenate([t[:, [0, 1]], t[:, [1, 2]], t[:, [2, 0]]], axis=0)
     e.sort(axis=1)
     key = e[:, 0] * np.int64(num_vertices) + e[:, 1]
-    uniq, counts = np.unique(key, return_counts=True)
+    uniq, inv = np.unique(key, return_inverse=True)
+    # a degenerate edge (a, a) is incremented twice by the reference (edges[a][a]++ twice), so it never counts as 1
+    counts = np.bincount(inv.reshape(-1), weights=np.where(e[:, 0] == e[:, 1], 2, 1), minlength=len(uniq))
     b = uniq[counts == 1]
     flags = np.zeros(num_vertices, dtype=np.uint8)
     flags[b // num_vertices] = 1
