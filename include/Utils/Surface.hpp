@@ -25,6 +25,7 @@ struct Triangle {  // reference include/Utils/Surface.hpp:11-23
 class Surface {
    public:
     std::vector<feab_mirror::vec3> vertices;  // :36
+    std::vector<feab_mirror::vec3> normals;   // :37  per-vertex normals (OBJ `vn`, or (0,1,0) for PSLG meshes)
     std::vector<float> values;                // :38  the field shown by the viewer / exported to .ply
     std::vector<Triangle> triangles;          // :39
     std::vector<bool> on_boundary;            // :40
@@ -52,6 +53,7 @@ inline void Surface::finish_init() {
             uint64_t a = t[e], b = t[(e + 1) % 3];
             if (a > b) std::swap(a, b);
             edges.push_back((a << 32) | b);
+            if (a == b) edges.push_back((a << 32) | b);  // the reference increments edges[a][a] twice: never a boundary edge
         }
     }
     std::sort(edges.begin(), edges.end());

@@ -1,7 +1,9 @@
 // Headless C++ host program written the way the reference's Application drives a solver (reference
 // src/Application.cpp:61-67 construct, :593-596 load surface, :722 brush, :530-540 advance_time + instability check),
 // but with CUDASolver (include/FEM/CUDASolver.hpp -> C ABI -> libfeab.so).  Used by tests/test_cpp_host.py:
-//   cuda_solver_driver mesh.bin <equation 0..3> <bc 0|1> <nsteps> <real_bytes 4|8> out.bin
+//   cuda_solver_driver mesh.bin <equation 0..3> <bc 0|1> <nsteps> <real_bytes 4|8> out.bin [export.ply threshold mesh_type]
+// With the three optional arguments the final field is also exported the way Application::export_to_ply does (reference
+// src/Application.cpp:680-690), through CUDASurface, taking the values from the solver device-to-device.
 // mesh.bin: int64 V, int64 T, int64 S, float xyz[3V], uint32 tri[3T], int64 seeds[S]
 // out.bin : float values[nsteps][V] (surface->values after every step), then int32 unstable flag per step
 #include <cstdint>
@@ -11,6 +13,7 @@
 #include <vector>
 
 #include "FEM/CUDASolver.hpp"
+#include "Utils/CUDASurface.hpp"
 
 static void die(const char* m) {
     std::fprintf(stderr, "cuda_solver_driver: %s\n", m);
@@ -18,7 +21,7 @@ static void die(const char* m) {
 }
 
 int main(int argc, char** argv) {
-    if (argc != 7) die("usage: mesh.bin equation bc nsteps real_bytes out.bin");
+    if (argc != 7 && argc != 10) die("usage: mesh.bin equation bc nsteps real_bytes out.bin [export.ply threshold mesh_type]");
     const int eq = std::atoi(argv[2]), bc = std::atoi(argv[3]), nsteps = std::atoi(argv[4]), real_bytes = std::atoi(argv[5]);
     FILE* f = std::fopen(argv[1], "rb");
     if (!f) die("cannot open mesh file");
@@ -64,6 +67,18 @@ int main(int argc, char** argv) {
     }
     std::fwrite(unstable.data(), 4, unstable.size(), out);
     std::fclose(out);
+    if (argc == 10) {
+        try {
+            const std::vector<bool> host_flags = surface->on_boundary;
+            CUDASurface dev(surface);          // normals empty -> (0,1,0), what init_from_PSLG sets
+            dev.detect_boundary();             // device pass must agree with the host mirror's finish_init()
+            if (surface->on_boundary != host_flags) die("device boundary flags differ from the host mirror");
+            dev.export_to_ply_from(std::static_pointer_cast<CUDASolver>(solver)->handle(), argv[7], 0.25f, (float)std::atof(argv[8]),
+                                   std::atoi(argv[9]));
+        } catch (const std::exception& e) {
+            die(e.what());
+        }
+    }
     std::printf("ok V=%lld unknowns=%u max_row=%u\n", (long long)V, fem_ctx->num_unknowns(), fem_ctx->num_max_nonzeros_per_row());
     return 0;
 }

@@ -29,7 +29,8 @@ def test_cuda_solver_header_compiles_against_reference_headers(tmp_path):
     """Inside the reference tree the reference's own FEM/Solver.hpp, FEMContext.hpp and Utils/Surface.hpp are found
     first; CUDASolver.hpp must compile against them unchanged."""
     src = tmp_path / "t.cpp"
-    src.write_text('#include "FEM/CUDASolver.hpp"\n'
+    src.write_text('#include "FEM/CUDASolver.hpp"\n#include "Utils/CUDASurface.hpp"\n'
+                   "void g(std::shared_ptr<Surface> s) { CUDASurface d(s); d.detect_boundary(); d.export_to_ply(\"x.ply\"); }\n"
                    "int main() { std::shared_ptr<FEMContext> c; std::shared_ptr<Solver> s = std::make_shared<CUDASolver>(c); return s ? 0 : 1; }\n")
     inc = [f"-I{REF}/include", f"-I{REF}/lib", f"-I{REF}/lib/glad/include", f"-I{REF}/lib/glm", f"-I{REF}/lib/eigen", f"-I{ROOT}/include"]
     out = subprocess.run(["g++", "-std=c++20", "-fpermissive", "-w", "-fsyntax-only", *inc, "-H", str(src)], capture_output=True, text=True)
@@ -76,3 +77,31 @@ def test_cpp_cuda_solver_matches_oracle(tmp_path, name, bc, eq):
         D.step(1)
         assert rel_l2(vals[s], D.get_values()) <= 1e-8, (s, rel_l2(vals[s], D.get_values()))
         assert bool(unstable[s]) == bool(D.unstable())
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mesh_type", [0, 2])
+def test_cpp_export_to_ply_equals_reference(tmp_path, mesh_type):
+    """The C++ host path end to end: CUDASolver steps, CUDASurface exports the field device-to-device; the file equals
+    the one the unmodified reference writes for the same float values."""
+    from oracle import surface_oracle as S
+    if not S.available():
+        pytest.skip("oracle/_ref/libfea_surface_ref.so not built")
+    exe = fbuild.CPP_DRIVER
+    xyz, tri = meshes.disk(8)
+    V = len(xyz)
+    nsteps = 4
+    _write_mesh(tmp_path / "m.bin", xyz, tri, meshes.seed_nodes(V))
+    ply = str(tmp_path / "o.ply")
+    out = subprocess.run([exe, str(tmp_path / "m.bin"), "0", "1", str(nsteps), "8", str(tmp_path / "o.bin"), ply, "0.002", str(mesh_type)],
+                         capture_output=True, text=True)
+    assert out.returncode == 0, out.stdout + out.stderr
+    vals = np.fromfile(tmp_path / "o.bin", dtype=np.float32)[:nsteps * V].reshape(nsteps, V)[-1]
+    R = S.RefSurface()
+    R.set_mesh(xyz, None, tri)
+    R.set_values(vals)
+    ref = str(tmp_path / "r.ply")
+    R.export_to_ply(ref, 0.25, 0.002, mesh_type)
+    got = open(ply, "rb").read()
+    assert got == open(ref, "rb").read()
+    assert int(got.split(b"element vertex ")[1].split(b"\n")[0]) > 0
