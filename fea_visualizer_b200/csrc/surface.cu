@@ -9,6 +9,7 @@
 
 #include "../../include/feab_surface.h"
 #include "ply_kernels.cuh"
+#include "pick_kernels.cuh"
 #include "ply_writer.hpp"
 #include "surface_kernels.cuh"
 
@@ -160,6 +161,14 @@ public:
         SCK(cudaStreamSynchronize(stream_));
     }
 
+    void get_values(float* v) {
+        need_mesh();
+        SREQ(v, FEAB_EINVAL, "get_values: null");
+        use();
+        SCK(cudaMemcpyAsync(v, d_val_.p, V_ * sizeof(float), cudaMemcpyDeviceToHost, stream_));
+        SCK(cudaStreamSynchronize(stream_));
+    }
+
     void set_color_map(const float* c21) {
         SREQ(c21, FEAB_EINVAL, "set_color_map: null");
         std::memcpy(cm_.c, c21, sizeof(cm_.c));
@@ -193,6 +202,36 @@ public:
         if (out) SCK(cudaMemcpyAsync(out, d_snrm_.p, 3 * V_ * sizeof(float), cudaMemcpyDeviceToHost, stream_));
         SCK(cudaStreamSynchronize(stream_));
         stamp();
+    }
+
+    // N4: returns the picked triangle (or -1); with do_brush also writes `value` into values[closest corner]
+    void pick(const float* o, const float* d, bool do_brush, float value, int* tri_idx, int* node, float* point3, float* dist) {
+        need_mesh();
+        SREQ(o && d, FEAB_EINVAL, "pick: null ray");
+        use();
+        d_pick_.alloc(2);
+        d_pick_out_.alloc(8);
+        const F3 origin{o[0], o[1], o[2]}, dir{d[0], d[1], d[2]};
+        SCK(cudaEventRecord(ev0_, stream_));
+        SCK(cudaMemsetAsync(d_pick_.p, 0xff, sizeof(unsigned long long), stream_));
+        if (T_) pick_kernel<<<cdiv(T_, kBlock), kBlock, 0, stream_>>>(d_xyz_.p, d_tri_.p, T_, origin, dir, d_pick_.p);
+        brush_apply<<<1, 1, 0, stream_>>>(d_xyz_.p, d_tri_.p, origin, dir, d_pick_.p, value, do_brush ? d_val_.p : nullptr,
+                                          (int*)d_pick_out_.p, d_pick_out_.p + 2);
+        launches_ += 2;
+        SCK(cudaGetLastError());
+        SCK(cudaEventRecord(ev1_, stream_));
+        float h[8];
+        SCK(cudaMemcpyAsync(h, d_pick_out_.p, sizeof(h), cudaMemcpyDeviceToHost, stream_));
+        SCK(cudaStreamSynchronize(stream_));
+        stamp();
+        int ih[2];
+        std::memcpy(ih, h, sizeof(ih));
+        if (node) *node = ih[0];
+        if (tri_idx) *tri_idx = ih[1];
+        if (ih[1] >= 0) {
+            if (point3) std::memcpy(point3, h + 2, 3 * sizeof(float));
+            if (dist) *dist = h[5];
+        }
     }
 
     template <typename IN>
@@ -315,6 +354,8 @@ private:
     Buf<uint32_t> d_tri_;
     Buf<uint8_t> d_onb_;
     Buf<long long> d_tsum_, d_total_;
+    Buf<unsigned long long> d_pick_;
+    Buf<float> d_pick_out_;
     ColorCoeffs cm_;
     // last ply_build result
     Buf<float> d_opos_, d_oval_, d_ocol_;
@@ -393,6 +434,7 @@ int feas_get_counts(const FeasHandle* h, int64_t* V, int64_t* T, int64_t* nb) {
 }
 int feas_get_mesh(FeasHandle* h, float* xyz, float* nrm, uint32_t* tri, uint8_t* onb) { FEAS_TRY(h, h->impl->get_mesh(xyz, nrm, tri, onb)); }
 int feas_set_values(FeasHandle* h, const float* v) { FEAS_TRY(h, h->impl->set_values(v, false)); }
+int feas_get_values(FeasHandle* h, float* v) { FEAS_TRY(h, h->impl->get_values(v)); }
 int feas_set_values_device(FeasHandle* h, const float* v) { FEAS_TRY(h, h->impl->set_values(v, true)); }
 int feas_set_color_map(FeasHandle* h, const float* c21) { FEAS_TRY(h, h->impl->set_color_map(c21)); }
 int feas_color_map(FeasHandle* h, int64_t n, const float* t, float* rgb) { FEAS_TRY(h, h->impl->color_map(n, t, rgb)); }
@@ -403,6 +445,12 @@ int feas_ply_build(FeasHandle* h, float ve, float thr, int mesh_type, int64_t* n
 int feas_ply_fetch(FeasHandle* h, float* pos, float* val, float* col, uint32_t* tri) { FEAS_TRY(h, h->impl->ply_fetch(pos, val, col, tri)); }
 int feas_export_ply(FeasHandle* h, const char* path, float ve, float thr, int mesh_type) {
     FEAS_TRY(h, h->impl->export_ply(path, ve, thr, mesh_type));
+}
+int feas_pick(FeasHandle* h, const float* o, const float* d, int* tri_idx, float* point3, float* dist) {
+    FEAS_TRY(h, h->impl->pick(o, d, false, 0.0f, tri_idx, nullptr, point3, dist));
+}
+int feas_brush(FeasHandle* h, const float* o, const float* d, float value, int* node) {
+    FEAS_TRY(h, h->impl->pick(o, d, true, value, nullptr, node, nullptr, nullptr));
 }
 int feas_last_ms(const FeasHandle* h, double* ms, int64_t* launches) {
     if (!h) return FEAB_EINVAL;

@@ -16,8 +16,8 @@ MESH_OPEN, MESH_CLOSED, MESH_MIRRORED = 0, 1, 2     # include/Utils/Surface.hpp:
 # every symbol include/feab_surface.h declares (checked by tests/test_abi.py without a GPU)
 ABI_SYMBOLS = [
     "feas_create", "feas_destroy", "feas_last_error", "feas_set_mesh", "feas_detect_boundary", "feas_load_obj", "feas_get_counts",
-    "feas_get_mesh", "feas_set_values", "feas_set_values_device", "feab_values_device", "feas_set_color_map", "feas_color_map",
-    "feas_smooth_normals", "feas_ply_build", "feas_ply_fetch", "feas_export_ply", "feas_last_ms",
+    "feas_get_mesh", "feas_set_values", "feas_get_values", "feas_set_values_device", "feab_values_device", "feas_set_color_map", "feas_color_map",
+    "feas_smooth_normals", "feas_pick", "feas_brush", "feas_ply_build", "feas_ply_fetch", "feas_export_ply", "feas_last_ms",
 ]
 
 
@@ -107,6 +107,27 @@ class DeviceSurface:
     def calculate_normals(self, vertex_extrusion):
         out = np.empty((self.counts()[0], 3), np.float32)
         self._ck(self.lib.feas_smooth_normals(self.h, C.c_float(vertex_extrusion), _p(out)))
+        return out
+
+    # -- picking / brush (BVH::ray_triangle_intersection, Application::brush) --
+    def pick(self, origin, direction):
+        o = np.ascontiguousarray(origin, dtype=np.float32)
+        d = np.ascontiguousarray(direction, dtype=np.float32)
+        tri, dist = C.c_int(-1), C.c_float(0.0)
+        pt = np.zeros(3, np.float32)
+        self._ck(self.lib.feas_pick(self.h, _p(o), _p(d), C.byref(tri), _p(pt), C.byref(dist)))
+        return tri.value, pt, dist.value
+
+    def brush(self, origin, direction, value):
+        o = np.ascontiguousarray(origin, dtype=np.float32)
+        d = np.ascontiguousarray(direction, dtype=np.float32)
+        node = C.c_int(-1)
+        self._ck(self.lib.feas_brush(self.h, _p(o), _p(d), C.c_float(value), C.byref(node)))
+        return node.value
+
+    def get_values(self):
+        out = np.empty(self.counts()[0], np.float32)
+        self._ck(self.lib.feas_get_values(self.h, _p(out)))
         return out
 
     # -- .ply --

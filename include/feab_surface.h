@@ -4,6 +4,8 @@
  *   N2  mesh ingest:     boundary-edge detection of Surface::init_from_obj        src/Utils/Surface.cpp:103-127
  *   N3  smooth normals:  shaders/FEM/smooth_normals.glsl:30-57, dispatched by
  *                        Surface::calculate_normals                                src/Utils/Surface.cpp:287-306
+ *   N4  brush / picking: BVH::ray_triangle_intersection + Application::brush      src/Utils/BVH.cpp:32-40, :182-216,
+ *                                                                                  src/Application.cpp:707-727
  *   N1  .ply exporter:   Surface::export_to_ply (threshold clipping, vertex
  *                        de-duplication, colour map) + ColorMap::get_color         src/Utils/Surface.cpp:138-285,
  *                                                                                  src/Utils/ColorMap.cpp:12-14
@@ -50,6 +52,7 @@ int feas_get_mesh(FeasHandle* h, float* xyz, float* normals, uint32_t* tri, uint
 
 /* Surface::values (include/Utils/Surface.hpp:38) */
 int feas_set_values(FeasHandle* h, const float* values);
+int feas_get_values(FeasHandle* h, float* values_out);
 /* Zero-copy hand-over from the solver: copies num_vertices floats device-to-device from `values_device`
  * (see feab_values_device below) on the Surface's stream. */
 int feas_set_values_device(FeasHandle* h, const float* values_device);
@@ -76,7 +79,16 @@ int feas_ply_build(FeasHandle* h, float vertex_extrusion, float threshold, int m
 int feas_ply_fetch(FeasHandle* h, float* positions, float* values, float* colors, uint32_t* tri);
 int feas_export_ply(FeasHandle* h, const char* path, float vertex_extrusion, float threshold, int mesh_type);
 
-/* measurement: device milliseconds of the last feas_ply_build / feas_detect_boundary / feas_smooth_normals (CUDA events
+/* N4 -- BVH::ray_triangle_intersection (src/Utils/BVH.cpp:32-40): nearest triangle hit by the ray with distance > 0,
+ * by the reference's own plane + three-edge test (:182-216), evaluated for every triangle on the device (no hierarchy).
+ * tri_idx = -1 when nothing is hit (point / distance untouched).  Exact distance ties go to the lowest triangle index. */
+int feas_pick(FeasHandle* h, const float* origin3, const float* direction3, int* tri_idx, float* point3, float* distance);
+/* Application::brush (src/Application.cpp:707-727): pick, then set Surface::values[node] = value for the corner of the hit
+ * triangle closest to the hit point (distance > 0).  node_out = that node or -1.  The caller forwards the write to the
+ * solver with feab_brush(solver, &node, 1, value), like Application does through surface->values. */
+int feas_brush(FeasHandle* h, const float* origin3, const float* direction3, float value, int* node_out);
+
+/* measurement: device milliseconds of the last feas_ply_build / feas_detect_boundary / feas_smooth_normals / feas_pick (CUDA events
  * on the Surface's stream), and the number of kernels this handle has launched */
 int feas_last_ms(const FeasHandle* h, double* ms, int64_t* kernel_launches);
 
