@@ -70,6 +70,18 @@ def main():
     byts = 12 * T + 28 * V + 12 * V + 9 * 4 * T
     rows.append({"row": "N3 smooth_normals", "ms": ms, "triangles_per_s": T / ms * 1e3, "algorithmic_bytes": byts, "GBps": byts / ms / 1e6,
                  "note": "events bracket the clear + the kernel; the D2H of the result is outside"})
+    # N4 picking: every triangle tested against one ray (read tri + gathered xyz)
+    org = np.array([0.3 * radius, 0.2 * radius, 3.0 * radius], np.float32)
+    dr = np.array([-0.05, 0.02, -1.0], np.float32)
+    dr /= np.linalg.norm(dr)
+    hit = {}
+
+    def pk():
+        hit["t"] = D.pick(org, dr)
+    ms = timed(pk)
+    byts = 12 * T + 12 * V
+    rows.append({"row": "N4 pick (brute force over all triangles)", "ms": ms, "triangles_per_s": T / ms * 1e3, "algorithmic_bytes": byts,
+                 "GBps": byts / ms / 1e6, "hit_triangle": hit["t"][0]})
     # N1 ply build (device only)
     for mt, thr in ((MESH_OPEN, 0.5), (MESH_CLOSED, 0.5), (MESH_OPEN, -10.0)):
         res = {}

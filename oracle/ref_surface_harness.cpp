@@ -4,6 +4,7 @@
 //   /root/reference/src/Utils/Surface.cpp    (OBJ ingest + boundary-edge detection :58-133, .ply exporter :138-285,
 //                                             PSLG triangulation hand-off :25-51, :431-486)
 //   /root/reference/src/Utils/ColorMap.cpp   (6th-order polynomial colour map :12-14)
+//   /root/reference/src/Utils/BVH.cpp        (median-split BVH + ray / triangle test used by the brush :8-216)
 //   /root/reference/src/Utils/PSLG.cpp, Shader.cpp, Mesh.cpp, lib/glad/src/glad.c, lib/triangle/triangle.cpp
 // compiled where they lie (oracle/Makefile, target _ref/libfea_surface_ref.so).  Nothing from the reference is copied.
 //
@@ -26,6 +27,7 @@
 #include <type_traits>
 #include <vector>
 
+#include "Utils/BVH.hpp"
 #include "Utils/ColorMap.hpp"
 #include "Utils/PSLG.hpp"
 #include "Utils/Surface.hpp"
@@ -63,6 +65,7 @@ void install_gl_noops() {
 
 struct SrfHandle {
     std::shared_ptr<Surface> surface;
+    std::shared_ptr<BVH> bvh;
     std::string err;
 };
 
@@ -202,6 +205,49 @@ int srf_export_to_ply(void* p, const char* path, float vertex_extrusion, float t
         return -1;
     }
     return 0;
+}
+
+// BVH::BVH(surface, max_depth) (src/Utils/BVH.cpp:8-16); Application uses settings.bvh_depth = 10 (include/Application.hpp:43)
+void srf_bvh_build(void* p, int max_depth) {
+    auto* h = static_cast<SrfHandle*>(p);
+    h->bvh = std::make_shared<BVH>(h->surface, max_depth);
+}
+
+// BVH::ray_triangle_intersection (src/Utils/BVH.cpp:32-40)
+int srf_pick(void* p, const float* o, const float* d, float* point3, float* dist) {
+    auto* h = static_cast<SrfHandle*>(p);
+    RayTriangleIntersection r = h->bvh->ray_triangle_intersection(glm::vec3(o[0], o[1], o[2]), glm::vec3(d[0], d[1], d[2]));
+    if (r.tri_idx != -1) {
+        std::memcpy(point3, &r.point, 12);
+        *dist = r.distance;
+    }
+    return r.tri_idx;
+}
+
+// Application::brush (src/Application.cpp:707-727) RESTATED: Application.cpp itself drags in the whole GUI and is not
+// compiled here.  Same statements, on the reference's own BVH result and Surface members.
+int srf_brush(void* p, const float* o, const float* d, float value) {
+    auto* h = static_cast<SrfHandle*>(p);
+    Surface& surface = *h->surface;
+    RayTriangleIntersection intersection = h->bvh->ray_triangle_intersection(glm::vec3(o[0], o[1], o[2]), glm::vec3(d[0], d[1], d[2]));
+    int point_idx = -1;
+    if (intersection.tri_idx != -1) {
+        float min_point_dist = 0.0f;
+        for (int i = 0; i < 3; i++) {
+            float dist = glm::distance(surface.vertices[surface.triangles[intersection.tri_idx][i]], intersection.point);
+            if ((point_idx == -1 || dist < min_point_dist) && dist > 0.0f) {
+                min_point_dist = dist;
+                point_idx = i;
+            }
+        }
+        if (point_idx != -1) surface.values[surface.triangles[intersection.tri_idx][point_idx]] = value;
+    }
+    return point_idx != -1 ? (int)surface.triangles[intersection.tri_idx][point_idx] : -1;
+}
+
+void srf_get_values(void* p, float* out) {
+    Surface& s = *static_cast<SrfHandle*>(p)->surface;
+    std::memcpy(out, s.values.data(), s.values.size() * sizeof(float));
 }
 
 }  // extern "C"

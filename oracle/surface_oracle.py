@@ -55,6 +55,10 @@ class RefSurface:
         L.srf_get_mesh.argtypes = [C.c_void_p] + [C.c_void_p] * 4
         L.srf_set_values.argtypes = [C.c_void_p, C.c_void_p]
         L.srf_export_to_ply.argtypes = [C.c_void_p, C.c_char_p, C.c_float, C.c_float, C.c_int]
+        L.srf_bvh_build.argtypes = [C.c_void_p, C.c_int]
+        L.srf_pick.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.srf_brush.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float]
+        L.srf_get_values.argtypes = [C.c_void_p, C.c_void_p]
         self.L = L
         self.h = C.c_void_p(L.srf_create())
 
@@ -115,6 +119,27 @@ class RefSurface:
         v = np.ascontiguousarray(v, dtype=np.float32)
         assert len(v) == self.counts()[0]
         self.L.srf_set_values(self.h, v.ctypes.data)
+
+    def bvh_build(self, max_depth=10):
+        self.L.srf_bvh_build(self.h, max_depth)
+
+    def pick(self, origin, direction):
+        o = np.ascontiguousarray(origin, dtype=np.float32)
+        d = np.ascontiguousarray(direction, dtype=np.float32)
+        pt = np.zeros(3, np.float32)
+        dist = C.c_float(0.0)
+        t = self.L.srf_pick(self.h, o.ctypes.data, d.ctypes.data, pt.ctypes.data, C.addressof(dist))
+        return t, pt, dist.value
+
+    def brush(self, origin, direction, value):
+        o = np.ascontiguousarray(origin, dtype=np.float32)
+        d = np.ascontiguousarray(direction, dtype=np.float32)
+        return self.L.srf_brush(self.h, o.ctypes.data, d.ctypes.data, value)
+
+    def get_values(self):
+        out = np.empty(self.counts()[0], np.float32)
+        self.L.srf_get_values(self.h, out.ctypes.data)
+        return out
 
     def export_to_ply(self, path, vertex_extrusion=0.25, threshold=0.0, mesh_type=MESH_OPEN):
         if self.L.srf_export_to_ply(self.h, os.fsencode(path), vertex_extrusion, threshold, mesh_type) != 0:

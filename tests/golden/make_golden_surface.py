@@ -10,6 +10,8 @@ Contents
   ply_<mesh>_<type>_<k>       bytes of the .ply Surface::export_to_ply writes, for mesh_type in {0,1,2} and the
                               (vertex_extrusion, threshold) pairs in CASES
   cm_<name>_t/_rgb            ColorMap::get_color samples for three of the reference's maps
+  pick_<mesh>_*               200 seeded rays through the reference BVH (depth 10, include/Application.hpp:43): hit triangle,
+                              point, distance (BVH::ray_triangle_intersection) and the node Application::brush would paint
   obj_icosphere_*             the bundled assets/fem_meshes/icosphere.obj after init_from_obj: counts and a checksum
 """
 import os
@@ -46,6 +48,20 @@ def surface_cases():
     return out
 
 
+def pick_rays(xyz, n=200, seed=7):
+    """Rays from a shell around the mesh towards jittered points of it (most hit), plus a few that miss."""
+    rng = np.random.default_rng(seed)
+    c = xyz.mean(0)
+    r = float(np.linalg.norm(xyz - c, axis=1).max())
+    o = rng.normal(size=(n, 3))
+    o = (c + 3.0 * r * o / np.linalg.norm(o, axis=1, keepdims=True)).astype(np.float32)
+    tgt = xyz[rng.integers(0, len(xyz), n)] + rng.normal(scale=0.05 * r, size=(n, 3))
+    tgt[::10] += 5.0 * r                                    # misses
+    d = tgt - o
+    d = (d / np.linalg.norm(d, axis=1, keepdims=True)).astype(np.float32)
+    return o, d
+
+
 def write_obj(path, xyz, nrm, tri):
     with open(path, "w") as f:
         for p in xyz:
@@ -79,6 +95,19 @@ def main():
                 p = os.path.join(tmp, "o.ply")
                 R2.export_to_ply(p, ve, thr, mt)
                 data[f"ply_{name}_{mt}_{k}"] = np.frombuffer(open(p, "rb").read(), dtype=np.uint8)
+    for name in ("ico6d", "disk"):
+        xyz, nrm, tri, val = surface_cases()[name]
+        R = S.RefSurface()
+        R.set_mesh(xyz, nrm, tri)
+        R.bvh_build(10)
+        o, d = pick_rays(xyz)
+        res = [R.pick(o[i], d[i]) for i in range(len(o))]
+        data[f"pick_{name}_o"], data[f"pick_{name}_d"] = o, d
+        data[f"pick_{name}_tri"] = np.array([r[0] for r in res], np.int32)
+        data[f"pick_{name}_point"] = np.array([r[1] for r in res], np.float32)
+        data[f"pick_{name}_dist"] = np.array([r[2] for r in res], np.float32)
+        data[f"pick_{name}_node"] = np.array([R.brush(o[i], d[i], 1.0 + i) for i in range(len(o))], np.int32)
+        data[f"pick_{name}_values"] = R.get_values()
     t = np.concatenate([np.linspace(-0.25, 1.25, 301), [0.0, 1.0, 0.5, 1e-20, -0.0]]).astype(np.float32)
     for cm, coeffs in S.COLOR_MAPS.items():
         R = S.RefSurface()

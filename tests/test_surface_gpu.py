@@ -206,3 +206,55 @@ def test_smooth_normals_vs_restatement(ve):
     want = S.smooth_normals(xyz, nrm, val, tri, ve)
     scale = np.abs(want).max()
     assert np.abs(got - want).max() <= 1e-5 * scale     # summation order only
+
+
+# ------------------------------------------------------------------------------------------------- N4: picking / brush
+@pytest.mark.parametrize("name", ["ico6d", "disk"])
+def test_pick_and_brush_equal_reference_bvh(name):
+    g = load_golden("ref_surface.npz")
+    D = DeviceSurface()
+    D.set_mesh(g[f"{name}_xyz"], g[f"{name}_nrm"], g[f"{name}_tri"])
+    o, d = g[f"pick_{name}_o"], g[f"pick_{name}_d"]
+    hits = 0
+    for i in range(len(o)):
+        t, pt, dist = D.pick(o[i], d[i])
+        assert t == int(g[f"pick_{name}_tri"][i]), i
+        if t >= 0:
+            hits += 1
+            assert (bits(pt) == bits(g[f"pick_{name}_point"][i])).all() and bits([dist])[0] == bits([g[f"pick_{name}_dist"][i]])[0], i
+        assert D.brush(o[i], d[i], 1.0 + i) == int(g[f"pick_{name}_node"][i]), i
+    assert hits > 100
+    assert (bits(D.get_values()) == bits(g[f"pick_{name}_values"])).all()      # the painted field, brush after brush
+
+
+@needs_ref
+def test_pick_equals_compiled_reference_200k_triangles():
+    from tests.golden.make_golden_surface import pick_rays
+    xyz, tri = meshes.icosphere(100, displace=True)
+    R = S.RefSurface()
+    R.set_mesh(xyz, xyz, tri)
+    R.bvh_build(10)
+    D = DeviceSurface()
+    D.set_mesh(xyz, xyz, tri)
+    o, d = pick_rays(xyz, n=300, seed=11)
+    for i in range(len(o)):
+        rt, rp, rd = R.pick(o[i], d[i])
+        t, pt, dist = D.pick(o[i], d[i])
+        assert t == rt, i
+        if t >= 0:
+            assert (bits(pt) == bits(rp)).all() and bits([dist])[0] == bits([rd])[0]
+        assert D.brush(o[i], d[i], 0.5) == R.brush(o[i], d[i], 0.5)
+
+
+def test_pick_ignores_hits_behind_the_origin_and_degenerate_triangles():
+    xyz = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0], [0, 0, 2], [1, 0, 2], [0, 1, 2], [5, 5, 5]], np.float32)
+    tri = np.array([[0, 1, 2], [3, 4, 5], [6, 6, 6]], np.uint32)                   # z = 0, z = 2, and a degenerate one
+    D = DeviceSurface()
+    D.set_mesh(xyz, None, tri)
+    t, pt, dist = D.pick([0.2, 0.2, 1.0], [0, 0, 1])                               # from between the two: only z = 2 is ahead
+    assert t == 1 and dist == 1.0 and pt.tolist() == [np.float32(0.2), np.float32(0.2), 2.0]
+    assert D.pick([0.2, 0.2, 3.0], [0, 0, 1])[0] == -1                             # both behind
+    assert D.pick([0.2, 0.2, -1.0], [0, 0, 1])[0] == 0                             # nearest of two
+    assert D.pick([0.2, 0.2, -1.0], [1, 0, 0])[0] == -1                            # parallel: |denom| <= 1e-6
+    assert D.brush([0.9, 0.05, -1.0], [0, 0, 1], 7.0) == 1                         # closest corner of triangle 0
+    assert D.get_values()[1] == 7.0
