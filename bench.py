@@ -224,9 +224,8 @@ def main():
         print(json.dumps({"error": "no CUDA device: libfeab has no CPU fallback"}))
         return 1
     if world > 1:
-        # NCCL prints "NCCL version ..." on STDOUT at NCCL_DEBUG=VERSION; stdout carries exactly one JSON line
-        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-            os.environ["NCCL_DEBUG"] = "WARN"
+        # NCCL writes its banner / debug lines ("NCCL version ...") to STDOUT by default; stdout carries exactly one JSON line
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     torch.cuda.set_device(local_rank)
 

@@ -12,6 +12,10 @@ Contents
   cm_<name>_t/_rgb            ColorMap::get_color samples for three of the reference's maps
   pick_<mesh>_*               200 seeded rays through the reference BVH (depth 10, include/Application.hpp:43): hit triangle,
                               point, distance (BVH::ray_triangle_intersection) and the node Application::brush would paint
+  pslg_*                      a 48-gon through the reference's own PSLG hand-off (Surface::init_from_PSLG -> Triangle "Qeqpza0.004",
+                              src/Utils/Surface.cpp:25-51, :431-486): vertices, triangles (winding reversed), point-marker
+                              boundary flags, and surface->values after 20 advection-diffusion / heat steps of the unmodified
+                              CPUSolver (oracle/_ref/libfea_ref.so) on that mesh
   obj_icosphere_*             the bundled assets/fem_meshes/icosphere.obj after init_from_obj: counts and a checksum
 """
 import os
@@ -108,6 +112,22 @@ def main():
         data[f"pick_{name}_dist"] = np.array([r[2] for r in res], np.float32)
         data[f"pick_{name}_node"] = np.array([R.brush(o[i], d[i], 1.0 + i) for i in range(len(o))], np.int32)
         data[f"pick_{name}_values"] = R.get_values()
+    from oracle import oracle as O
+    th = np.linspace(0, 2 * np.pi, 48, endpoint=False)
+    R = S.RefSurface()
+    R.init_from_pslg(np.stack([1.3 * np.cos(th), 1.3 * np.sin(th)], 1), 0.004)
+    xyz, _, tri, ob = R.get_mesh()
+    data["pslg_xyz"], data["pslg_tri"], data["pslg_onb"] = xyz, tri, ob
+    seeds = meshes.seed_nodes(len(xyz))
+    for eq in (0, 2):
+        X = O.Reference(xyz, tri, ob, 0)
+        X.clear()
+        X.set_equation(eq)
+        v = np.zeros(len(xyz), np.float32)
+        v[seeds] = 1.0
+        X.set_values(v)
+        X.step(20)
+        data[f"pslg_values_eq{eq}"] = X.get_values()
     t = np.concatenate([np.linspace(-0.25, 1.25, 301), [0.0, 1.0, 0.5, 1e-20, -0.0]]).astype(np.float32)
     for cm, coeffs in S.COLOR_MAPS.items():
         R = S.RefSurface()

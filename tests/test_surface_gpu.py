@@ -258,3 +258,38 @@ def test_pick_ignores_hits_behind_the_origin_and_degenerate_triangles():
     assert D.pick([0.2, 0.2, -1.0], [1, 0, 0])[0] == -1                            # parallel: |denom| <= 1e-6
     assert D.brush([0.9, 0.05, -1.0], [0, 0, 1], 7.0) == 1                         # closest corner of triangle 0
     assert D.get_values()[1] == 7.0
+
+
+# ------------------------------------------------------------------------------------------------- PSLG hand-off
+@pytest.mark.parametrize("eq", [0, 2])
+def test_reference_pslg_mesh_through_the_solver(eq):
+    """A mesh produced by the reference's own PSLG hand-off (Surface::init_from_PSLG -> Triangle, winding reversed,
+    point-marker boundary flags; fixture from the compiled reference) solved on the device: fp32 build vs the unmodified
+    fp32 CPUSolver's field after 20 steps, fp64 build vs the fp64 oracle; the device boundary pass agrees with Triangle's
+    point markers on this simply connected domain."""
+    from oracle import oracle as O
+    from tests.util import rel_l2
+    g = load_golden("ref_surface.npz")
+    xyz, tri, ob = g["pslg_xyz"], g["pslg_tri"], g["pslg_onb"]
+    V = len(xyz)
+    D = DeviceSurface()
+    D.set_mesh(xyz, None, tri)
+    assert (D.detect_boundary()[0] == ob).all()
+    v0 = np.zeros(V, np.float32)
+    v0[meshes.seed_nodes(V)] = 1.0
+    out = {}
+    for real in (32, 64):
+        F = feab.Feab(real=real)
+        F.set_mesh(xyz, tri, ob)
+        F.clear()
+        F.set_equation(eq)
+        F.set_values(v0)
+        F.step(20)
+        out[real] = F.get_values()
+    assert rel_l2(out[32], g[f"pslg_values_eq{eq}"]) <= 2e-5          # fp32 vs fp32 Eigen, 20 steps (drift bar of DESIGN.md 5)
+    X = O.Oracle(xyz, tri, ob, 0, real=64)
+    X.clear()
+    X.set_equation(eq)
+    X.set_values(v0)
+    X.step(20)
+    assert rel_l2(out[64], X.get_values()) <= 1e-7                     # fp64 vs fp64 oracle through float32 surface->values
