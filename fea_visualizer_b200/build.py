@@ -9,7 +9,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libfeab.so")
 SOURCES = ["feab.cu", "surface.cu", "ply_writer.cpp"]
-HEADERS = ["common.cuh", "pattern.cuh", "assembly.cuh", "solver.cuh", "bicgstab.cuh", "spmv_tma.cuh", "comm.cuh", "partition.cuh", "pcg_persistent.cuh", "surface_kernels.cuh", "ply_kernels.cuh", "pick_kernels.cuh", "ply_writer.hpp",
+HEADERS = ["common.cuh", "pattern.cuh", "assembly.cuh", "solver.cuh", "bicgstab.cuh", "spmv_tma.cuh", "comm.cuh", "partition.cuh", "pcg_persistent.cuh", "rhs_tma.cuh", "surface_kernels.cuh", "ply_kernels.cuh", "pick_kernels.cuh", "ply_writer.hpp",
            os.path.join("..", "..", "include", "feab_surface.h"),
            os.path.join("..", "..", "include", "feab.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC,-ffp-contract=off", "-shared"]

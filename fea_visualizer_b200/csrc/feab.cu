@@ -20,6 +20,7 @@
 #include "partition.cuh"
 #include "pattern.cuh"
 #include "pcg_persistent.cuh"
+#include "rhs_tma.cuh"
 #include "solver.cuh"
 #include "spmv_tma.cuh"
 
@@ -161,6 +162,13 @@ class SolverT final : public SolverBase {
         cm_.loc = d_loc_;
         if (const char* v = getenv("FEAB_SPMV")) spmv_variant_ = atoi(v);
         if (const char* v = getenv("FEAB_PREFETCH_X")) prefetch_x_ = atoi(v);
+        if (const char* v = getenv("FEAB_RHS_TMA")) rhs_tma_ = atoi(v) != 0;
+        {
+            using RCfg = TmaCfg<R, kRhsRows, kRhsCpr, kRhsStages>;
+            CK(cudaFuncSetAttribute(rhs_init_tma<R, 0, kRhsRows, kRhsCpr, kRhsStages, kRhsMinB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RCfg::kSmemBytes));
+            CK(cudaFuncSetAttribute(rhs_init_tma<R, 2, kRhsRows, kRhsCpr, kRhsStages, kRhsMinB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RCfg::kSmemBytes));
+            CK(cudaFuncSetAttribute(rhs_init_tma<R, 3, kRhsRows, kRhsCpr, kRhsStages, kRhsMinB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RCfg::kSmemBytes));
+        }
         setup_spmv_variants();
         // persistent whole-solve kernel (pcg_persistent.cuh): same tile geometry as SpMV variant 4
         using PCfg = TmaCfg<R, kPcgRows, kPcgCpr, kPcgStages>;
@@ -774,6 +782,38 @@ class SolverT final : public SolverBase {
     //      host-batched mode, and driven in lock-step over several handles by feab_mg_group_step) ----
     int first_halo_tile(int rows_per_tile) const { return world_ > 1 ? (int)(n_int_ / rows_per_tile) : INT32_MAX; }
 
+    // K6: RHS + PCG start.  Heat / advection-diffusion / Gray-Scott stream M/dt through the TMA ring (rhs_tma.cuh); the wave
+    // equation (two value arrays) and FEAB_RHS_TMA=0 use the LDG kernel of solver.cuh.  Same bits either way.
+    static constexpr int kRhsRows = 512, kRhsCpr = 8, kRhsStages = 2, kRhsMinB = 2;
+    template <int EQ>
+    void launch_rhs_tma(cudaStream_t s, const StepScalars& sc, R* prt, const Comm& cm) {
+        using Cfg = TmaCfg<R, kRhsRows, kRhsCpr, kRhsStages>;
+        const int nt = std::max(1, cdiv64(n_, kRhsRows));
+        const int grid = std::max(1, std::min({nt, kRhsMinB * sms_, g_tile_}));
+        rhs_init_tma<R, EQ, kRhsRows, kRhsCpr, kRhsStages, kRhsMinB><<<grid, kRhsRows, Cfg::kSmemBytes, s>>>(
+            d_rowptr_.p, d_col_.p, d_Md_.p, d_u_.p, d_v_.p, d_dinv0_.p, d_dinv1_.p, n_, nt, sc, d_r_[0].p, d_p_[0].p, d_r_[1].p, d_p_[1].p, prt,
+            g_tile_, cm);
+    }
+    void launch_rhs(cudaStream_t s, const StepScalars& sc, R* prt, const Comm& cm) {
+        const size_t sm2 = 2 * kTileCap * sizeof(R);
+#define FEAB_RHS(EQ)                                                                                                             \
+    rhs_init<R, EQ><<<g_tile_, kBlock, sm2, s>>>(d_rowptr_.p, d_col_.p, d_Md_.p, d_K_.p, d_u_.p, d_v_.p, d_dinv0_.p, d_dinv1_.p, n_, \
+                                                 num_tiles_, sc, d_r_[0].p, d_p_[0].p, d_r_[1].p, d_p_[1].p, prt, cm)
+        switch (eq_) {
+            case FEAB_EQ_HEAT:
+                if (rhs_tma_) launch_rhs_tma<0>(s, sc, prt, cm); else FEAB_RHS(0);
+                break;
+            case FEAB_EQ_WAVE: FEAB_RHS(1); break;
+            case FEAB_EQ_ADVECTION_DIFFUSION:
+                if (rhs_tma_) launch_rhs_tma<2>(s, sc, prt, cm); else FEAB_RHS(2);
+                break;
+            default:
+                if (rhs_tma_) launch_rhs_tma<3>(s, sc, prt, cm); else FEAB_RHS(3);
+                break;
+        }
+#undef FEAB_RHS
+    }
+
     void ph_push_state(cudaStream_t s) {  // ghosts of u, v and the surface values of boundary rows -> neighbours
         if (world_ == 1) return;
         state_push<R><<<1, 1024, 0, s>>>(cm_, hp_, d_u_.p, d_v_.p, d_values_.p);
@@ -782,22 +822,11 @@ class SolverT final : public SolverBase {
     void ph_step_begin(cudaStream_t s, bool capturing) {
         const int gV = cdiv64(V_, kBlock);
         const StepScalars sc = scalars();
-        const size_t sm2 = 2 * kTileCap * sizeof(R);
         if (world_ > 1) wait_kernel<<<1, 32, 0, s>>>(cm_, hp_, 1);
         CK(cudaMemsetAsync(d_unstable_, 0, sizeof(int), s));
         R* target = eq_ == FEAB_EQ_REACTION_DIFFUSION ? d_v_.p : d_u_.p;
         gather_values<R><<<gV, kBlock, 0, s>>>(d_values_.p, colmap_p_, V_, target);
-        R* prt = part_rhs();
-#define FEAB_RHS(EQ)                                                                                                            \
-    rhs_init<R, EQ><<<g_tile_, kBlock, sm2, s>>>(d_rowptr_.p, d_col_.p, d_Md_.p, d_K_.p, d_u_.p, d_v_.p, d_dinv0_.p, d_dinv1_.p, n_, \
-                                                 num_tiles_, sc, d_r_[0].p, d_p_[0].p, d_r_[1].p, d_p_[1].p, prt, cm_)
-        switch (eq_) {
-            case FEAB_EQ_HEAT: FEAB_RHS(0); break;
-            case FEAB_EQ_WAVE: FEAB_RHS(1); break;
-            case FEAB_EQ_ADVECTION_DIFFUSION: FEAB_RHS(2); break;
-            default: FEAB_RHS(3); break;
-        }
-#undef FEAB_RHS
+        launch_rhs(s, sc, part_rhs(), cm_);
         if (!capturing) launches_ += 2;
         CK(cudaGetLastError());
     }
@@ -1136,18 +1165,7 @@ class SolverT final : public SolverBase {
                     cg_direction<R><<<g_vec_, kBlock, 0, stream_>>>(d_r_[0].p, d_p_[0].p, d_dinv0_.p, n_, d_st_, part_rr(), part_rz(), g_vec_, none, 0, one);
                     break;
                 default:
-                    if (eq_ == FEAB_EQ_REACTION_DIFFUSION)
-                        rhs_init<R, 3><<<g_tile_, kBlock, 2 * kTileCap * sizeof(R), stream_>>>(d_rowptr_.p, d_col_.p, d_Md_.p, d_K_.p, d_u_.p, d_v_.p,
-                                                                                               d_dinv0_.p, d_dinv1_.p, n_, num_tiles_, sc, d_r_[0].p,
-                                                                                               d_p_[0].p, d_r_[1].p, d_p_[1].p, part_rhs(), one);
-                    else if (eq_ == FEAB_EQ_WAVE)
-                        rhs_init<R, 1><<<g_tile_, kBlock, 2 * kTileCap * sizeof(R), stream_>>>(d_rowptr_.p, d_col_.p, d_Md_.p, d_K_.p, d_u_.p, d_v_.p,
-                                                                                               d_dinv0_.p, d_dinv1_.p, n_, num_tiles_, sc, d_r_[0].p,
-                                                                                               d_p_[0].p, d_r_[1].p, d_p_[1].p, part_rhs(), one);
-                    else
-                        rhs_init<R, 0><<<g_tile_, kBlock, 2 * kTileCap * sizeof(R), stream_>>>(d_rowptr_.p, d_col_.p, d_Md_.p, d_K_.p, d_u_.p, d_v_.p,
-                                                                                               d_dinv0_.p, d_dinv1_.p, n_, num_tiles_, sc, d_r_[0].p,
-                                                                                               d_p_[0].p, d_r_[1].p, d_p_[1].p, part_rhs(), one);
+                    launch_rhs(stream_, sc, part_rhs(), one);
                     break;
             }
         };
@@ -1393,6 +1411,7 @@ class SolverT final : public SolverBase {
 
     // persistent whole-solve kernel
     int pcg_max_grid_ = 0;
+    bool rhs_tma_ = true;
     unsigned long long* d_bar_ = nullptr;
     unsigned long long* d_prof_ = nullptr;  // FEAB_PCG_PROF=1: phase timers of the persistent kernel (CTA 0)
     DevBuf<R> d_ppart_;
