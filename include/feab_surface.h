@@ -1,4 +1,4 @@
-/* feab_surface.h -- C ABI of the rows either side of the time-stepping hot path (SURVEY.md section 8(f), N1-N3):
+/* feab_surface.h -- C ABI of the rows either side of the time-stepping hot path (SURVEY.md section 8(f), N1-N4):
  * the device-resident mirror of the reference's `Surface` object (include/Utils/Surface.hpp:34-73).
  *
  *   N2  mesh ingest:     boundary-edge detection of Surface::init_from_obj        src/Utils/Surface.cpp:103-127
