@@ -170,7 +170,29 @@ def cpu_reference(sample_nu, steps, warmup, threads, target_rows=None):
 
 
 # ------------------------------------------------------------------------------------------------ main
+_REAL_STDOUT = None
+
+
+def claim_stdout():
+    """stdout carries exactly ONE JSON line: native libraries (NCCL prints "NCCL version ..." with printf) get fd 2 instead."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def main():
+    claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
@@ -200,7 +222,7 @@ def main():
         warm = max(1, min(args.warmup, 2))
         res = cpu_reference(args.cpu_nu, max(1, min(args.steps, 5)), warm, ncores, target_rows=V_target)
         if res is None:
-            print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref not built"}))
+            emit({"impl": "reference", "unavailable": "oracle/_ref not built"})
             return 0
         val = res["converted_steps_per_s"]
         line = {"metric": "gray_scott_timesteps_per_s", "value": val, "unit": "steps/s", "n_gpus": args.gpus, "steps": args.steps,
@@ -213,7 +235,7 @@ def main():
                                            f"({res['sample_rows']} rows), converted by {res['conversion']}; {res['build']}"},
                 "e2e": {"value": val, "unit": "steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                 "gpu_launches": 0}
-        print(json.dumps(line))
+        emit(line)
         return 0
 
     import torch
@@ -221,11 +243,9 @@ def main():
     from fea_visualizer_b200 import feab
 
     if not torch.cuda.is_available():
-        print(json.dumps({"error": "no CUDA device: libfeab has no CPU fallback"}))
+        emit({"error": "no CUDA device: libfeab has no CPU fallback"})
         return 1
     if world > 1:
-        # NCCL writes its banner / debug lines ("NCCL version ...") to STDOUT by default; stdout carries exactly one JSON line
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     torch.cuda.set_device(local_rank)
 
@@ -361,7 +381,7 @@ def main():
                            "setup_s": setup_s},
                 "e2e": {"value": total_steps / (e2e_ms_max / 1e3), "unit": "steps/s", "h2d_bytes_per_step": 4 * V, "d2h_bytes_per_step": 4 * V},
                 "gpu_launches": launches_all, "pcg_phase_profile": prof, "roofline": roof, "cpu_baseline": cpu, "clocks": clocks}
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
     return 0
