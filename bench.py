@@ -307,7 +307,9 @@ def main():
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        F.step_ptr(host.data_ptr(), 1, True)  # H2D of values, one step, D2H of values, synchronised
+        # one GPU: H2D of values, one step, D2H of values, synchronised.  Partitioned: surface->values lives on rank 0's host
+        # (FEAB_SYNC_ROOT): rank 0 uploads, NVLink forwards to the peers, only rank 0 downloads the result
+        F.step_ptr(host.data_ptr(), 1, feab.SYNC_ROOT if world > 1 else feab.SYNC_FULL)
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
     barrier()
@@ -379,7 +381,8 @@ def main():
                            "tolerance": "eps of dtype (Eigen default)" if args.tol < 0 else args.tol,
                            "pcg_iterations_last_step": its, "loop": args.loop, "l2_policy": "inputs larger than L2 (matrix + vectors >> 126 MB)",
                            "setup_s": setup_s},
-                "e2e": {"value": total_steps / (e2e_ms_max / 1e3), "unit": "steps/s", "h2d_bytes_per_step": 4 * V, "d2h_bytes_per_step": 4 * V},
+                "e2e": {"value": total_steps / (e2e_ms_max / 1e3), "unit": "steps/s", "h2d_bytes_per_step": 4 * V, "d2h_bytes_per_step": 4 * V,
+                        "mode": "host buffers on rank 0 (FEAB_SYNC_ROOT), peers fed over NVLink" if world > 1 else "host buffers, full sync"},
                 "gpu_launches": launches_all, "pcg_phase_profile": prof, "roofline": roof, "cpu_baseline": cpu, "clocks": clocks}
         emit(line)
     if world > 1:

@@ -32,11 +32,13 @@ struct CommCtrl {  // written by peers
     unsigned long long halo_flag[kMaxRanks];   // [source rank] number of direction-halo pushes received
     unsigned long long state_flag[kMaxRanks];  // [source rank] number of end-of-step state pushes received
     unsigned long long full_flag[kMaxRanks];   // [source rank] number of full value broadcasts received
-    unsigned long long pad[8];
+    unsigned long long root_flag;              // number of root pushes (rank 0's full surface->values) received
+    unsigned long long pad[7];
 };
 struct CommLocal {  // private to the rank
     unsigned long long ar_seq;
     unsigned long long halo_seq, state_seq, full_seq;
+    unsigned long long root_seq;
     unsigned int ticket;
     int error;
 };
@@ -310,6 +312,45 @@ __global__ void __launch_bounds__(kBlock) values_broadcast(Comm cm, HaloPlan hp,
         cm.loc->full_seq = s;
         for (int q = 0; q < cm.world; q++)
             if (q != cm.rank) st_release_sys(&cm.ctrl[q]->full_flag[cm.rank], s);
+    }
+}
+
+// FEAB_SYNC_ROOT (feab.h): surface->values lives on the host of rank 0 only (the viewer process).  Rank 0 uploads it and
+// pushes the whole array into every peer's mirror over NVLink; the peers wait for the flag instead of touching PCIe.
+// Grid-wide, coalesced float4 stores; the last CTA raises the flags.
+__global__ void __launch_bounds__(kBlock) root_push(Comm cm, HaloPlan hp, int64_t V, const float* __restrict__ values) {
+    const int64_t nv4 = V / 4;
+    const float4* src = reinterpret_cast<const float4*>(values);
+    for (int q = 0; q < cm.world; q++) {
+        if (q == cm.rank) continue;
+        float* dstf = reinterpret_cast<float*>(hp.base[q] + hp.off_vec[kVecValues][q]);
+        float4* dst = reinterpret_cast<float4*>(dstf);
+        for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nv4; i += (int64_t)gridDim.x * blockDim.x) dst[i] = src[i];
+        if (blockIdx.x == 0)
+            for (int64_t i = nv4 * 4 + threadIdx.x; i < V; i += blockDim.x) dstf[i] = values[i];
+    }
+    __threadfence_system();
+    __shared__ int s_last;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned t = atomicAdd(&cm.loc->ticket, 1u);
+        s_last = (t == gridDim.x - 1) ? 1 : 0;
+    }
+    __syncthreads();
+    if (s_last && threadIdx.x == 0) {
+        cm.loc->ticket = 0;
+        __threadfence_system();
+        const unsigned long long s = cm.loc->root_seq + 1;
+        cm.loc->root_seq = s;
+        for (int q = 0; q < cm.world; q++)
+            if (q != cm.rank) st_release_sys(&cm.ctrl[q]->root_flag, s);
+    }
+}
+__global__ void root_wait(Comm cm) {
+    if (threadIdx.x == 0) {
+        const unsigned long long s = cm.loc->root_seq + 1;
+        cm.loc->root_seq = s;
+        spin_until_ge(&cm.ctrl[cm.rank]->root_flag, s, cm.loc);
     }
 }
 

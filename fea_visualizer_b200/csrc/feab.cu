@@ -1039,7 +1039,21 @@ class SolverT final : public SolverBase {
         REQUIRE(!lockstep_, FEAB_EINVAL, "step: this handle belongs to a lock-step group (use feab_mg_group_step)");
         CK(cudaSetDevice(device_));
         CK(cudaEventRecord(ev0_, stream_));
-        if (values) CK(cudaMemcpyAsync(d_values_.p, values, V_ * sizeof(float), cudaMemcpyHostToDevice, stream_));
+        // FEAB_SYNC_ROOT on a partitioned handle: only rank 0 touches PCIe; its array reaches the peers over NVLink.
+        // Safe against the previous call: rank 0 gets here only after its wait for every peer's values_broadcast of
+        // that call, i.e. after the peers' last read of their mirrors.
+        const bool root_mode = world_ > 1 && sync == FEAB_SYNC_ROOT && values != nullptr;
+        if (root_mode) {
+            if (rank_ == 0) {
+                CK(cudaMemcpyAsync(d_values_.p, values, V_ * sizeof(float), cudaMemcpyHostToDevice, stream_));
+                root_push<<<std::max(1, std::min(cdiv64(V_ / 4, kBlock), sms_ * 4)), kBlock, 0, stream_>>>(cm_, hp_, V_, d_values_.p);
+            } else {
+                root_wait<<<1, 32, 0, stream_>>>(cm_);
+            }
+            launches_++;
+        } else if (values) {
+            CK(cudaMemcpyAsync(d_values_.p, values, V_ * sizeof(float), cudaMemcpyHostToDevice, stream_));
+        }
         if (n_ > 0 && nsteps > 0) {
             ensure_operator();
             ph_push_state(stream_);
@@ -1059,7 +1073,7 @@ class SolverT final : public SolverBase {
         }
         if (values && sync) {
             ph_broadcast_values(stream_);
-            CK(cudaMemcpyAsync(values, d_values_.p, V_ * sizeof(float), cudaMemcpyDeviceToHost, stream_));
+            if (!root_mode || rank_ == 0) CK(cudaMemcpyAsync(values, d_values_.p, V_ * sizeof(float), cudaMemcpyDeviceToHost, stream_));
         }
         CK(cudaEventRecord(ev1_, stream_));
         CK(cudaStreamSynchronize(stream_));

@@ -19,6 +19,7 @@ MAT_MASS, MAT_STIFFNESS, MAT_ADVECTION = 0, 1, 2
 SOLVER_PARITY_CG, SOLVER_BICGSTAB = 0, 1
 ASSEMBLY_SCATTER, ASSEMBLY_ORDERED = 0, 1
 LOOP_GRAPH_WHILE, LOOP_HOST_BATCHED, LOOP_PERSISTENT = 0, 1, 2
+SYNC_NONE, SYNC_FULL, SYNC_ROOT = 0, 1, 2
 
 # every symbol include/feab.h declares (checked by tests/test_abi.py without a GPU)
 ABI_SYMBOLS = [
@@ -195,11 +196,11 @@ class Feab:
             self._ck(self.lib.feab_step(self.h, None, C.c_int(nsteps), C.c_int(0)))
         else:
             assert values.dtype == np.float32 and values.flags.c_contiguous and values.shape[0] == self.V
-            self._ck(self.lib.feab_step(self.h, C.c_void_p(values.ctypes.data), C.c_int(nsteps), C.c_int(1 if sync_values else 0)))
+            self._ck(self.lib.feab_step(self.h, C.c_void_p(values.ctypes.data), C.c_int(nsteps), C.c_int(int(sync_values))))   # FEAB_SYNC_*
 
     def step_ptr(self, host_ptr: int, nsteps: int, sync_values: bool):
         """Same with a raw host pointer (e.g. pinned torch memory)."""
-        self._ck(self.lib.feab_step(self.h, C.c_void_p(host_ptr), C.c_int(nsteps), C.c_int(1 if sync_values else 0)))
+        self._ck(self.lib.feab_step(self.h, C.c_void_p(host_ptr), C.c_int(nsteps), C.c_int(int(sync_values))))   # FEAB_SYNC_*: 0 none, 1 full, 2 root
 
     def unstable(self):
         f = C.c_int()

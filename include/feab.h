@@ -45,6 +45,10 @@ enum { FEAB_ASSEMBLY_SCATTER = 0, FEAB_ASSEMBLY_ORDERED = 1 };
  * GRAPH_WHILE: one CUDA graph per step with a device-side WHILE node around three kernels per iteration.
  * HOST_BATCHED: the same three kernels launched in batches with a flag poll per batch.  BiCGSTAB uses GRAPH_WHILE
  * when PERSISTENT is selected. */
+/* feab_step's sync_values.  ROOT only differs from FULL on a partitioned (multi-GPU) handle: surface->values lives on the
+ * host of rank 0 (the viewer process); rank 0 uploads it and forwards it to the peers over NVLink, the peers ignore their
+ * values_inout and touch no PCIe, and only rank 0 receives the result. */
+enum { FEAB_SYNC_NONE = 0, FEAB_SYNC_FULL = 1, FEAB_SYNC_ROOT = 2 };
 enum { FEAB_LOOP_GRAPH_WHILE = 0, FEAB_LOOP_HOST_BATCHED = 1, FEAB_LOOP_PERSISTENT = 2 };
 
 enum {
@@ -132,7 +136,7 @@ int feab_brush(FeabHandle* h, const int64_t* nodes, int64_t count, float strengt
 /* Solver::advance_time (src/FEM/CPUSolver.cpp:64-147), nsteps times.
  * values_inout != NULL: copied host->device before the first step (the brush may have written it) and, when
  * sync_values != 0, device->host after the last one -- the reference's data contract through surface->values.
- * values_inout == NULL keeps everything device-resident (benchmark mode). */
+ * values_inout == NULL keeps everything device-resident (benchmark mode).  sync_values: FEAB_SYNC_*. */
 int feab_step(FeabHandle* h, float* values_inout, int nsteps, int sync_values);
 /* Solver::has_numerical_instability (src/FEM/CPUSolver.cpp:41-48): any u_i > 1e4 or v_i > 1e4 */
 int feab_unstable(FeabHandle* h, int* out);

@@ -6,6 +6,7 @@ Every rank owns one GPU and one partition of the same mesh; halos and all-reduce
 memory inside the solver kernels (csrc/comm.cuh).  Checked on every rank, for all four equations, in both loop modes:
   * the fields after each of 5 steps against the fp64 oracle (<= 1e-8 relative L2, the north star's per-step bar),
   * surface->values complete and identical on every rank after a synchronising step (the reference's data contract),
+  * FEAB_SYNC_ROOT: values in and out through rank 0's host array only,
   * a multi-step device-resident call == the same steps one at a time.
 Prints "MP_PARTITIONED_OK world=N" on rank 0 and exits 0; any failure exits non-zero on that rank.
 """
@@ -82,6 +83,18 @@ def main():
                     t0 = t.clone()
                     dist.broadcast(t0, 0)
                     assert bool((t == t0).all()), (name, eq, s, "values differ between ranks")
+                # FEAB_SYNC_ROOT: only rank 0's host array is read and written; the peers' arrays are ignored and left alone
+                root_in = host.copy() if rank == 0 else np.full(V, -7.0, np.float32)
+                F.step(1, values=root_in, sync_values=feab.SYNC_ROOT)
+                D.set_values(host)
+                D.step(1)
+                if rank == 0:
+                    e = rel_l2(root_in, D.get_values())
+                    assert e <= 1e-8, (name, bc, loop, eq, "root mode", e)
+                else:
+                    assert (root_in == -7.0).all(), "root mode wrote into a peer's host array"
+                e = rel_l2(gather_state(F, 0, idx_map, row_node, n), D.get_state(0))
+                assert e <= 1e-8, (name, bc, loop, eq, "root mode state", e)
                 # K steps in one device-resident call == K single steps (bitwise on the owners' rows)
                 F.step(3)
                 D.step(3)
