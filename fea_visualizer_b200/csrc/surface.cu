@@ -452,6 +452,26 @@ int feas_pick(FeasHandle* h, const float* o, const float* d, int* tri_idx, float
 int feas_brush(FeasHandle* h, const float* o, const float* d, float value, int* node) {
     FEAS_TRY(h, h->impl->pick(o, d, true, value, nullptr, node, nullptr, nullptr));
 }
+int feas_write_ply(const char* path, int64_t nv, const float* pos, const float* col, int64_t nt, const uint32_t* tri) {
+    if (!path || nv < 0 || nt < 0 || (nv > 0 && (!pos || !col)) || (nt > 0 && !tri)) return FEAB_EINVAL;
+    std::string e;
+    return feas::write_ply(path, nv, pos, col, nt, tri, e) ? FEAB_OK : FEAB_EINVAL;
+}
+int feas_parse_obj(const char* path, int64_t* nv, int64_t* nt, float* xyz, float* nrm, uint32_t* tri) {
+    if (!path) return FEAB_EINVAL;
+    feas::ObjMesh m;
+    std::string e;
+    if (!feas::load_obj(path, m, e)) {
+        g_feas_create_err = e;
+        return FEAB_EINVAL;
+    }
+    if (nv) *nv = (int64_t)m.xyz.size() / 3;
+    if (nt) *nt = (int64_t)m.tri.size() / 3;
+    if (xyz) std::memcpy(xyz, m.xyz.data(), m.xyz.size() * sizeof(float));
+    if (nrm) std::memcpy(nrm, m.nrm.data(), m.nrm.size() * sizeof(float));
+    if (tri) std::memcpy(tri, m.tri.data(), m.tri.size() * sizeof(uint32_t));
+    return FEAB_OK;
+}
 int feas_last_ms(const FeasHandle* h, double* ms, int64_t* launches) {
     if (!h) return FEAB_EINVAL;
     if (ms) *ms = h->impl->last_ms();

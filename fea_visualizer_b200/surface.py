@@ -17,12 +17,40 @@ MESH_OPEN, MESH_CLOSED, MESH_MIRRORED = 0, 1, 2     # include/Utils/Surface.hpp:
 ABI_SYMBOLS = [
     "feas_create", "feas_destroy", "feas_last_error", "feas_set_mesh", "feas_detect_boundary", "feas_load_obj", "feas_get_counts",
     "feas_get_mesh", "feas_set_values", "feas_get_values", "feas_set_values_device", "feab_values_device", "feas_set_color_map", "feas_color_map",
-    "feas_smooth_normals", "feas_pick", "feas_brush", "feas_ply_build", "feas_ply_fetch", "feas_export_ply", "feas_last_ms",
+    "feas_smooth_normals", "feas_pick", "feas_brush", "feas_ply_build", "feas_ply_fetch", "feas_export_ply", "feas_write_ply", "feas_parse_obj", "feas_last_ms",
 ]
 
 
 def _p(a):
     return None if a is None else C.c_void_p(a.ctypes.data)
+
+
+def write_ply(path, positions, colors, tri):
+    """Host-only: the ASCII writer of the exporter on ready-made arrays (no GPU, no handle)."""
+    lib = load_library()
+    pos = np.ascontiguousarray(positions, dtype=np.float32)
+    col = np.ascontiguousarray(colors, dtype=np.float32)
+    t = np.ascontiguousarray(tri, dtype=np.uint32)
+    rc = lib.feas_write_ply(os.fsencode(path), C.c_int64(len(pos)), _p(pos), _p(col), C.c_int64(len(t)), _p(t))
+    if rc != 0:
+        raise FeabError(rc, "feas_write_ply failed")
+
+
+def parse_obj(path):
+    """Host-only OBJ reader with the semantics of Surface::init_from_obj: (xyz, normals, tri)."""
+    lib = load_library()
+    lib.feas_last_error.restype = C.c_char_p
+    lib.feas_last_error.argtypes = [C.c_void_p]
+    nv, nt = C.c_int64(), C.c_int64()
+    rc = lib.feas_parse_obj(os.fsencode(path), C.byref(nv), C.byref(nt), None, None, None)
+    if rc != 0:
+        raise FeabError(rc, lib.feas_last_error(None).decode())
+    xyz, nrm = np.empty((nv.value, 3), np.float32), np.empty((nv.value, 3), np.float32)
+    tri = np.empty((nt.value, 3), np.uint32)
+    rc = lib.feas_parse_obj(os.fsencode(path), None, None, _p(xyz), _p(nrm), _p(tri))
+    if rc != 0:
+        raise FeabError(rc, lib.feas_last_error(None).decode())
+    return xyz, nrm, tri
 
 
 class DeviceSurface:

@@ -78,6 +78,12 @@ int feas_ply_build(FeasHandle* h, float vertex_extrusion, float threshold, int m
 /* positions / colors: num_out_vertices x 3 float; values: num_out_vertices; tri: num_out_triangles x 3; any may be NULL */
 int feas_ply_fetch(FeasHandle* h, float* positions, float* values, float* colors, uint32_t* tri);
 int feas_export_ply(FeasHandle* h, const char* path, float vertex_extrusion, float threshold, int mesh_type);
+/* The host half alone (no GPU involved, no handle): the ASCII writer of Surface::export_to_ply (src/Utils/Surface.cpp:263-285)
+ * on arrays that are already clipped / de-duplicated / coloured.  positions, colors: nv x 3; tri: nt x 3.  0 or FEAB_EINVAL. */
+int feas_write_ply(const char* path, int64_t nv, const float* positions, const float* colors, int64_t nt, const uint32_t* tri);
+/* The OBJ reader alone (host only): counts first (outputs NULL), then the arrays.  Semantics of Surface::init_from_obj :58-101.
+ * Returns FEAB_EINVAL for unreadable files, files without `v` or without `vn` lines (the reference throws). */
+int feas_parse_obj(const char* path, int64_t* num_vertices, int64_t* num_triangles, float* xyz, float* normals, uint32_t* tri);
 
 /* N4 -- BVH::ray_triangle_intersection (src/Utils/BVH.cpp:32-40): nearest triangle hit by the ray with distance > 0,
  * by the reference's own plane + three-edge test (:182-216), evaluated for every triangle on the device (no hierarchy).

@@ -105,3 +105,57 @@ def test_smooth_normals_restatement_on_a_sphere():
     big = S.smooth_normals(xyz, nrm, val + 100.0, tri, 0.25)
     two = S.smooth_normals((2 * xyz).astype(np.float32), nrm, val, tri, 0.25)
     assert np.allclose(big, two, rtol=1e-5, atol=1e-7)
+
+
+# ---------------------------------------------------------------------------------------- host halves of libfeab (no GPU)
+@pytest.mark.parametrize("name", ["ico6d", "grid"])
+def test_ascii_writer_reproduces_the_reference_bytes(name, tmp_path):
+    """feas_write_ply (std::to_chars shortest form) on the arrays parsed back from the reference's own files gives the
+    same bytes: the formatting half of the exporter is std::format("{}")-identical."""
+    fbuild.build()
+    g = load_golden("ref_surface.npz")
+    for mt in (0, 2):
+        for k in range(len(CASES)):
+            ref = g[f"ply_{name}_{mt}_{k}"].tobytes()
+            src = str(tmp_path / "ref.ply")
+            open(src, "wb").write(ref)
+            v, f = S.parse_ply(src)
+            out = str(tmp_path / "ours.ply")
+            surface.write_ply(out, v[:, :3], v[:, 3:], f)
+            assert open(out, "rb").read() == ref, (name, mt, k)
+
+
+def test_ascii_writer_float_forms(tmp_path):
+    # shortest round-trip digits; fixed vs scientific as std::to_chars chooses; negative zero; uint32 range
+    pos = np.array([[0.1, -0.0, 1e-5], [123456792.0, 1e10, 3.4028235e38], [1.0, 0.5, 1.1754944e-38]], np.float32)
+    col = np.array([[1 / 3, 2 / 3, 1.0], [0.0, 100.0, 1e-3], [16777216.0, 0.30000001192092896, 7.0]], np.float32)
+    tri = np.array([[0, 1, 2], [4294967295, 0, 7]], np.uint32)
+    out = str(tmp_path / "f.ply")
+    surface.write_ply(out, pos, col, tri)
+    body = open(out, "rb").read().split(b"end_header\n")[1].decode().split("\n")
+    assert body[0] == "0.1 -0 1e-05 0.33333334 0.6666667 1"
+    assert body[1] == "123456792 1e+10 3.4028235e+38 0 100 0.001"      # fixed form prints the exact integer
+    assert body[2] == "1 0.5 1.1754944e-38 16777216 0.3 7"
+    assert body[3] == "3 0 1 2" and body[4] == "3 4294967295 0 7"
+    v, _ = S.parse_ply(out)
+    assert (v.view(np.uint32) == np.hstack([pos, col]).view(np.uint32)).all()      # every float round-trips
+
+
+def test_obj_reader_matches_reference_ingest(tmp_path):
+    from tests.golden.make_golden_surface import write_obj
+    g = load_golden("ref_surface.npz")
+    for name in ("ico6d", "disk"):
+        p = str(tmp_path / (name + ".obj"))
+        write_obj(p, g[f"{name}_xyz"], g[f"{name}_nrm"], g[f"{name}_tri"])
+        xyz, nrm, tri = surface.parse_obj(p)
+        assert (xyz.view(np.uint32) == g[f"{name}_xyz"].view(np.uint32)).all() and (tri == g[f"{name}_tri"]).all()
+        assert (nrm.view(np.uint32) == g[f"{name}_objnrm"].view(np.uint32)).all()   # normalised sums, bit-exact vs the reference
+    # quads are fan-triangulated, negative indices are relative, files without normals are rejected like the reference does
+    q = tmp_path / "q.obj"
+    q.write_text("v 0 0 0\nv 1 0 0\nv 1 0 1\nv 0 0 1\nvn 0 1 0\nf -4//1 -3//1 -2//1 -1//1\n")
+    xyz, nrm, tri = surface.parse_obj(str(q))
+    assert tri.tolist() == [[0, 1, 2], [0, 2, 3]] and (nrm == [0, 1, 0]).all()
+    n = tmp_path / "n.obj"
+    n.write_text("v 0 0 0\nv 1 0 0\nv 0 1 0\nf 1 2 3\n")
+    with pytest.raises(feab.FeabError, match="does not contain normals"):
+        surface.parse_obj(str(n))
