@@ -20,6 +20,7 @@
 #include "partition.cuh"
 #include "pattern.cuh"
 #include "pcg_persistent.cuh"
+#include "pcg_dual.cuh"
 #include "rhs_tma.cuh"
 #include "solver.cuh"
 #include "spmv_tma.cuh"
@@ -192,8 +193,17 @@ class SolverT final : public SolverBase {
             opt_.loop_mode = FEAB_LOOP_PERSISTENT;
             d_ppart_.alloc((size_t)3 * pcg_max_grid_);
         }
+        // Gray-Scott: both solves of a step in lock-step from one index stream (pcg_dual.cuh); FEAB_DUAL=0/1 overrides
+        using DCfg = DualCfg<R, kDualRows, kPcgCpr, kPcgStages>;
+        CK(cudaFuncSetAttribute(pcg_dual<R, kDualRows, kPcgCpr, kPcgStages, kPcgMinB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DCfg::kSmemBytes));
+        int docc = 0;
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&docc, pcg_dual<R, kDualRows, kPcgCpr, kPcgStages, kPcgMinB>, 2 * kDualRows, DCfg::kSmemBytes));
+        dual_max_grid_ = coop ? docc * sms_ : 0;
+        if (dual_max_grid_ > 0) d_dpart_.alloc((size_t)6 * dual_max_grid_);
+        if (const char* v = getenv("FEAB_DUAL")) dual_ = atoi(v) != 0;
     }
     static constexpr int kPcgRows = 512, kPcgCpr = 8, kPcgStages = 2, kPcgMinB = 2;
+    static constexpr int kDualRows = 256;
 
     // ---- SpMV variants: 0 = LDG/CSR-stream (solver.cuh), 1.. = TMA pipelines (spmv_tma.cuh) ----
     template <int ROWS, int CPR, int STAGES, int MINB>
@@ -892,12 +902,51 @@ class SolverT final : public SolverBase {
     }
 
     // PCG solve of slot `slot` into x.  capturing: build WHILE node into the graph being captured on stream_.
-    void enqueue_pcg(int slot, const R* A, const R* dinv, R* x, bool capturing) {
+    bool dual_applies(bool capturing) const {
+        return dual_ && !capturing && opt_.loop_mode == FEAB_LOOP_PERSISTENT && eq_ == FEAB_EQ_REACTION_DIFFUSION && world_ == 1 && dual_max_grid_ > 0 &&
+               !use_bicgstab();
+    }
+    // Gray-Scott, one GPU: u- and v-solve advance together until the first of them stops (pcg_dual.cuh), then each is
+    // finished (or found finished) by the single-system kernel, which resumes from CgState.
+    void enqueue_dual(const R* const* A, const R* const* dinv, R* const* x) {
+        cudaGraphConditionalHandle none = 0;
+        ph_cg_begin(stream_, 0, x[0], none, 0);
+        ph_cg_begin(stream_, 1, x[1], none, 0);
+        CK(cudaMemsetAsync(d_bar_, 0, 4 * sizeof(unsigned long long), stream_));
+        PcgDualArgs<R> da;
+        da.rowptr = d_rowptr_.p;
+        da.col = d_col_.p;
+        for (int s = 0; s < 2; s++) {
+            da.A[s] = A[s];
+            da.dinv[s] = dinv[s];
+            da.x[s] = x[s];
+            da.r[s] = d_r_[s].p;
+            da.p[s] = d_p_[s].p;
+        }
+        da.y[0] = d_y_.p;
+        da.y[1] = d_w_[0].p;
+        da.n = n_;
+        da.num_tiles = std::max(1, cdiv64(n_, kDualRows));
+        da.st = d_st_;
+        da.part = d_dpart_.p;
+        da.bar = d_bar_;
+        const int grid = std::min(dual_max_grid_, da.num_tiles);
+        using DCfg = DualCfg<R, kDualRows, kPcgCpr, kPcgStages>;
+        void* kargs[] = {(void*)&da};
+        if (time_solves_) CK(cudaEventRecord(ev_solve_[0], stream_));
+        CK(cudaLaunchCooperativeKernel((const void*)pcg_dual<R, kDualRows, kPcgCpr, kPcgStages, kPcgMinB>, dim3(grid), dim3(2 * kDualRows), kargs,
+                                       DCfg::kSmemBytes, stream_));
+        launches_ += 3;  // 2 x cg_begin + pcg_dual
+        for (int slot = 0; slot < 2; slot++) enqueue_pcg(slot, A[slot], dinv[slot], x[slot], false, true);
+        if (time_solves_) CK(cudaEventRecord(ev_solve_[1], stream_));
+    }
+
+    void enqueue_pcg(int slot, const R* A, const R* dinv, R* x, bool capturing, bool resume = false) {
         CgState<R>* st = d_st_ + slot;
         if (!capturing && opt_.loop_mode == FEAB_LOOP_PERSISTENT) {
             // the whole solve is one cooperative launch: no WHILE node, no host polling (pcg_persistent.cuh)
             cudaGraphConditionalHandle none = 0;
-            ph_cg_begin(stream_, slot, x, none, 0);
+            if (!resume) ph_cg_begin(stream_, slot, x, none, 0);
             CK(cudaMemsetAsync(d_bar_ + 2 * slot, 0, 2 * sizeof(unsigned long long), stream_));
             PcgArgs<R> pa;
             pa.rowptr = d_rowptr_.p;
@@ -919,11 +968,11 @@ class SolverT final : public SolverBase {
             const int grid = std::min(pcg_max_grid_, pa.num_tiles);
             using PCfg = TmaCfg<R, kPcgRows, kPcgCpr, kPcgStages>;
             void* kargs[] = {(void*)&pa, (void*)&cm_, (void*)&hp_};
-            if (time_solves_) CK(cudaEventRecord(ev_solve_[2 * slot], stream_));
+            if (time_solves_ && !resume) CK(cudaEventRecord(ev_solve_[2 * slot], stream_));
             CK(cudaLaunchCooperativeKernel((const void*)pcg_persistent<R, kPcgRows, kPcgCpr, kPcgStages, kPcgMinB>, dim3(grid), dim3(kPcgRows), kargs,
                                            PCfg::kSmemBytes, stream_));
-            if (time_solves_) CK(cudaEventRecord(ev_solve_[2 * slot + 1], stream_));
-            launches_ += 2;
+            if (time_solves_ && !resume) CK(cudaEventRecord(ev_solve_[2 * slot + 1], stream_));
+            launches_ += resume ? 1 : 2;
             return;
         }
         if (capturing) {
@@ -978,7 +1027,11 @@ class SolverT final : public SolverBase {
             const R* dinv[2];
             R* x[2];
             const int ns = solves(A, dinv, x);
-            for (int slot = 0; slot < ns; slot++) enqueue_pcg(slot, A[slot], dinv[slot], x[slot], capturing);
+            dual_last_ = ns == 2 && dual_applies(capturing);
+            if (dual_last_)
+                enqueue_dual(A, dinv, x);
+            else
+                for (int slot = 0; slot < ns; slot++) enqueue_pcg(slot, A[slot], dinv[slot], x[slot], capturing);
         }
         ph_finish(stream_, capturing);
     }
@@ -1084,7 +1137,7 @@ class SolverT final : public SolverBase {
         if (n_ > 0 && nsteps > 0 && graph_mode_last_) account_graph_launches(nsteps);
         solve_ms_ = 0;
         if (time_solves_) {  // device time of the last step's persistent PCG kernels
-            const int ns = eq_ == FEAB_EQ_REACTION_DIFFUSION ? 2 : 1;
+            const int ns = eq_ == FEAB_EQ_REACTION_DIFFUSION && !dual_applies(false) ? 2 : 1;  // the dual path brackets both solves with one pair
             for (int sl = 0; sl < ns; sl++) {
                 float t = 0;
                 if (cudaEventElapsedTime(&t, ev_solve_[2 * sl], ev_solve_[2 * sl + 1]) == cudaSuccess) solve_ms_ += t;
@@ -1138,6 +1191,7 @@ class SolverT final : public SolverBase {
         s->last_call_steps = last_steps_;
         s->kernel_launches = launches_;
         s->solve_ms = solve_ms_;
+        s->shared_iterations = dual_last_ && !use_bicgstab() ? std::min(st[0].iter1, st[1].iter1) : 0;
     }
 
     // ---------------------------------------------------------------- measurement hook
@@ -1425,6 +1479,10 @@ class SolverT final : public SolverBase {
 
     // persistent whole-solve kernel
     int pcg_max_grid_ = 0;
+    int dual_max_grid_ = 0;
+    bool dual_ = true;   // FEAB_DUAL=0 runs the two Gray-Scott solves one after the other
+    bool dual_last_ = false;
+    DevBuf<R> d_dpart_;
     bool rhs_tma_ = true;
     unsigned long long* d_bar_ = nullptr;
     unsigned long long* d_prof_ = nullptr;  // FEAB_PCG_PROF=1: phase timers of the persistent kernel (CTA 0)

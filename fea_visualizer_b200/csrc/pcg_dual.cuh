@@ -1,0 +1,332 @@
+// Gray-Scott: the u-solve and the v-solve of one time step (CPUSolver.cpp:139-140) as ONE persistent kernel, for as long as
+// both are iterating.  Both right-hand sides are built from the old fields (:134-137) and A_u = M/dt + Du K, A_v = M/dt + Dv K
+// share rowptr / columns, so the two Jacobi-PCG recurrences (ConjugateGradient.h:30-85, each with its own alpha, beta and
+// stopping test) can advance in lock-step:
+//   * one index stream (rowptr + columns, 32 B/row) feeds both SpMVs: a 256-row tile is staged once together with BOTH value
+//     streams; threads 0..255 of the CTA multiply system 0, threads 256..511 system 1;
+//   * the three grid barriers of an iteration are shared.
+// Per shared iteration this moves 336 instead of 368 B/row and pays 3 instead of 6 barriers.  As soon as one system stops
+// (converged / maxit / non-finite), the kernel finishes the other one's iteration, stores its state and exits; the
+// single-system kernel (pcg_persistent.cuh) resumes it from CgState (abs_new[0], iter1).  Every operation on a system is
+// the one pcg_persistent performs; only the grouping of the per-CTA partial sums differs (256-row tiles), so results agree
+// with the other loop drivers to summation order, not bit for bit.  One GPU only (a partitioned handle runs the two solves
+// one after the other).
+#pragma once
+#include "pcg_persistent.cuh"
+
+namespace feab {
+
+template <typename R>
+struct PcgDualArgs {
+    const int* rowptr;
+    const int* col;
+    const R* A[2];
+    const R* dinv[2];
+    R* x[2];
+    R* r[2];
+    R* p[2];
+    R* y[2];
+    int64_t n;
+    int num_tiles;
+    CgState<R>* st;           // [2], prepared by cg_begin
+    R* part;                  // 6 x gridDim.x: pap0 | pap1 | rr0 | rr1 | rz0 | rz1
+    unsigned long long* bar;  // zero at launch
+};
+
+template <typename R, int ROWS, int CPR, int STAGES>
+struct DualCfg {
+    static constexpr int kCap = ROWS * CPR;
+    static constexpr size_t kValBytes = ((size_t)(kCap + 4) * sizeof(R) + 127) / 128 * 128;
+    static constexpr size_t kColBytes = ((size_t)(kCap + 4) * 4 + 127) / 128 * 128;
+    static constexpr size_t kRpBytes = ((size_t)(ROWS + 8) * 4 + 127) / 128 * 128;
+    static constexpr size_t kStageBytes = 2 * kValBytes + kColBytes + kRpBytes;
+    static constexpr size_t kSmemBytes = kStageBytes * STAGES + 128 + 128;
+};
+
+template <typename R, int ROWS, int CPR, int STAGES, int MINB>
+__global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a) {
+    using Cfg = DualCfg<R, ROWS, CPR, STAGES>;
+    using O = Ops<R>;
+    constexpr int NWT = 2 * ROWS / 32;  // warps per CTA
+    constexpr int NWH = ROWS / 32;      // warps per half
+    extern __shared__ unsigned char smraw_dual[];
+    unsigned char* base = reinterpret_cast<unsigned char*>(((uintptr_t)smraw_dual + 127) & ~(uintptr_t)127);
+    uint64_t* full = reinterpret_cast<uint64_t*>(base + Cfg::kStageBytes * STAGES);
+    __shared__ R red[NWT + 1];
+
+    if (a.st[0].done || a.st[1].done) return;  // cg_begin settled one of them: the single-system kernels take over (uniform)
+    R thr[2] = {a.st[0].thr, a.st[1].thr};
+    const int maxit = min(a.st[0].maxit, a.st[1].maxit);
+    R abs_old[2] = {a.st[0].abs_new[0], a.st[1].abs_new[0]};
+    const int64_t n = a.n;
+    const int num_tiles = a.num_tiles;
+    const int h = (int)threadIdx.x / ROWS;   // which system this thread multiplies
+    const int t = (int)threadIdx.x % ROWS;   // its row inside the tile
+
+    auto stage_val = [&](int s, int sys) { return reinterpret_cast<R*>(base + (size_t)s * Cfg::kStageBytes + (size_t)sys * Cfg::kValBytes); };
+    auto stage_col = [&](int s) { return reinterpret_cast<int*>(base + (size_t)s * Cfg::kStageBytes + 2 * Cfg::kValBytes); };
+    auto stage_rp = [&](int s) { return reinterpret_cast<int*>(base + (size_t)s * Cfg::kStageBytes + 2 * Cfg::kValBytes + Cfg::kColBytes); };
+
+    uint64_t policy = 0;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES; s++) mbar_init(&full[s], 1);
+        mbar_fence_init();
+        policy = l2_evict_first_policy();
+    }
+    __syncthreads();
+    auto issue = [&](int tile, int s) {  // thread 0 only
+        const int64_t r0 = (int64_t)tile * ROWS;
+        const int rows = (int)min((int64_t)ROWS, n - r0);
+        const int tb = a.rowptr[r0], te = a.rowptr[r0 + rows];
+        const int tba = tb & ~3;
+        const int cnt_al = ((te - tba) + 3) & ~3;
+        const uint32_t rp_b = (uint32_t)(((rows + 1 + 3) & ~3) * 4);
+        const bool staged = (te - tba) <= Cfg::kCap;
+        mbar_expect_tx(&full[s], rp_b + (staged ? (uint32_t)cnt_al * (uint32_t)(2 * sizeof(R) + 4) : 0u));
+        tma_load_1d(stage_rp(s), a.rowptr + r0, rp_b, &full[s], policy);
+        if (staged) {
+            tma_load_1d(stage_val(s, 0), a.A[0] + tba, (uint32_t)cnt_al * (uint32_t)sizeof(R), &full[s], policy);
+            tma_load_1d(stage_val(s, 1), a.A[1] + tba, (uint32_t)cnt_al * (uint32_t)sizeof(R), &full[s], policy);
+            tma_load_1d(stage_col(s), a.col + tba, (uint32_t)cnt_al * 4u, &full[s], policy);
+        }
+    };
+    unsigned fills = 0;
+    auto prologue = [&]() {
+        if (threadIdx.x == 0) {
+            int tl = blockIdx.x;
+            for (int s = 0; s < STAGES && tl < num_tiles; s++, tl += gridDim.x) issue(tl, (int)((fills + s) % STAGES));
+        }
+    };
+    prologue();
+
+    unsigned long long bar_target = 0;
+    const int G = (int)gridDim.x;
+    R* const part = a.part;
+    constexpr int N = Vec<R>::N;
+    const int64_t nvec = n / N;
+    const int64_t gthreads = (int64_t)gridDim.x * blockDim.x;
+    const int64_t gtid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const R* const Ah = a.A[h];
+    R* const ph = a.p[h];
+    R* const yh = a.y[h];
+
+    int it = a.st[0].iter1;
+    int iters[2] = {0, 0};
+    bool fin[2] = {false, false};
+    R rr[2] = {(R)0, (R)0};
+    while (true) {
+        // ---------------- phase A: y_s = A_s p_s for both systems from one staged index stream ----------------
+        R acc = (R)0;
+        int k = 0;
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, k++) {
+            const unsigned f = fills + (unsigned)k;
+            const int s = (int)(f % STAGES);
+            mbar_wait(&full[s], (f / STAGES) & 1u);
+            const int* rp = stage_rp(s);
+            const int64_t r0 = (int64_t)tile * ROWS;
+            const int rows = (int)min((int64_t)ROWS, n - r0);
+            const int tb = rp[0], te = rp[rows];
+            const int tba = tb & ~3;
+            const bool staged = (te - tba) <= Cfg::kCap;
+            if (t < rows) {
+                const int64_t r = r0 + t;
+                const int kb = rp[t], ke = rp[t + 1];
+                R ta = (R)0, tb2 = (R)0, xr = (R)0;
+                if (staged) {
+                    const R* sv = stage_val(s, h) + (kb - tba);
+                    const int* sc = stage_col(s) + (kb - tba);
+                    const int len = ke - kb;
+                    R av[8], xv[8];
+                    int cv[8];
+#pragma unroll
+                    for (int j = 0; j < 8; j++) {
+                        if (j < len) {
+                            cv[j] = sc[j];
+                            av[j] = sv[j];
+                        } else {
+                            cv[j] = (int)r;
+                            av[j] = (R)0;
+                        }
+                    }
+#pragma unroll
+                    for (int j = 0; j < 8; j++) xv[j] = ph[cv[j]];
+#pragma unroll
+                    for (int j = 0; j < 8; j++) {
+                        if (j < len) {
+                            if (j & 1)
+                                tb2 += av[j] * xv[j];
+                            else
+                                ta += av[j] * xv[j];
+                        }
+                    }
+                    xr = xv[7];
+                    if (len >= 8) {
+                        xr = ph[r];
+                        for (int j = 8; j < len; j++) {
+                            R pr = sv[j] * ph[sc[j]];
+                            if (j & 1)
+                                tb2 += pr;
+                            else
+                                ta += pr;
+                        }
+                    }
+                } else {
+                    int q = kb;
+                    for (; q + 1 < ke; q += 2) {
+                        ta += Ah[q] * ph[a.col[q]];
+                        tb2 += Ah[q + 1] * ph[a.col[q + 1]];
+                    }
+                    if (q < ke) ta += Ah[q] * ph[a.col[q]];
+                    xr = ph[r];
+                }
+                const R sum = ta + tb2;
+                yh[r] = sum;
+                acc += xr * sum;
+            }
+            __syncthreads();  // every consumer is done with stage s
+            if (threadIdx.x == 0) {
+                const int next = tile + STAGES * gridDim.x;
+                if (next < num_tiles) issue(next, s);
+            }
+        }
+        fills += (unsigned)k;
+        it++;
+        // per-half sums in a fixed order: warps [0, NWH) belong to system 0, [NWH, 2 NWH) to system 1
+        acc = warp_sum(acc);
+        if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+        __syncthreads();
+        if (threadIdx.x < 2) {
+            R s = (R)0;
+            for (int w = 0; w < NWH; w++) s += red[threadIdx.x * NWH + w];
+            part[(size_t)threadIdx.x * G + blockIdx.x] = s;
+        }
+        __syncthreads();
+        prologue();
+        grid_barrier(a.bar, bar_target);
+        R pap[2];
+        pap[0] = sum_cta_partials<R, NWT>(part, red);
+        pap[1] = sum_cta_partials<R, NWT>(part + G, red);
+
+        // ---------------- phase B (both systems): r -= alpha y, |r|^2, r.z ----------------
+        R alpha[2];
+#pragma unroll
+        for (int s = 0; s < 2; s++) {
+            alpha[s] = abs_old[s] / pap[s];
+            R prr = (R)0, prz = (R)0;
+            R* const rs = a.r[s];
+            const R* const ys = a.y[s];
+            const R* const ds = a.dinv[s];
+            for (int64_t i = gtid; i < nvec; i += gthreads) {
+                R rv[N], yv[N], dv[N];
+                vload<R>(rs + i * N, rv);
+                vload<R>(ys + i * N, yv);
+                vload<R>(ds + i * N, dv);
+#pragma unroll
+                for (int q = 0; q < N; q++) {
+                    rv[q] = O::sub(rv[q], O::mul(alpha[s], yv[q]));
+                    R z = O::mul(dv[q], rv[q]);
+                    prr += rv[q] * rv[q];
+                    prz += rv[q] * z;
+                }
+                vstore<R>(rs + i * N, rv);
+            }
+            if (blockIdx.x == 0) {
+                for (int64_t i = nvec * N + threadIdx.x; i < n; i += blockDim.x) {
+                    R rn = O::sub(rs[i], O::mul(alpha[s], ys[i]));
+                    rs[i] = rn;
+                    R z = O::mul(ds[i], rn);
+                    prr += rn * rn;
+                    prz += rn * z;
+                }
+            }
+            prr = block_sum_n<R, NWT>(prr, red);
+            __syncthreads();
+            prz = block_sum_n<R, NWT>(prz, red);
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                part[(size_t)(2 + s) * G + blockIdx.x] = prr;
+                part[(size_t)(4 + s) * G + blockIdx.x] = prz;
+            }
+        }
+        grid_barrier(a.bar, bar_target);
+        R rz[2];
+#pragma unroll
+        for (int s = 0; s < 2; s++) {
+            rr[s] = sum_cta_partials<R, NWT>(part + (size_t)(2 + s) * G, red);
+            rz[s] = sum_cta_partials<R, NWT>(part + (size_t)(4 + s) * G, red);
+        }
+        // ---------------- stopping tests (ConjugateGradient.h:72-73), per system; direction update for the ones that go on ----
+#pragma unroll
+        for (int s = 0; s < 2; s++) {
+            const bool conv = rr[s] < thr[s];
+            fin[s] = conv || it >= maxit || !(rr[s] <= O::huge());
+            R* const xs = a.x[s];
+            R* const ps = a.p[s];
+            if (fin[s]) {
+                iters[s] = conv ? it - 1 : it;
+                if (!conv) abs_old[s] = rz[s];
+                for (int64_t i = gtid; i < nvec; i += gthreads) {  // the deferred x += alpha p of the last iteration
+                    R xv[N], pv[N];
+                    vload<R>(xs + i * N, xv);
+                    vload<R>(ps + i * N, pv);
+#pragma unroll
+                    for (int q = 0; q < N; q++) xv[q] = O::add(xv[q], O::mul(alpha[s], pv[q]));
+                    vstore<R>(xs + i * N, xv);
+                }
+                if (blockIdx.x == 0)
+                    for (int64_t i = nvec * N + threadIdx.x; i < n; i += blockDim.x) xs[i] = O::add(xs[i], O::mul(alpha[s], ps[i]));
+            } else {
+                const R beta = rz[s] / abs_old[s];
+                abs_old[s] = rz[s];
+                const R* const rs = a.r[s];
+                const R* const ds = a.dinv[s];
+                for (int64_t i = gtid; i < nvec; i += gthreads) {
+                    R xv[N], rv[N], pv[N], dv[N];
+                    vload<R>(xs + i * N, xv);
+                    vload<R>(rs + i * N, rv);
+                    vload<R>(ps + i * N, pv);
+                    vload<R>(ds + i * N, dv);
+#pragma unroll
+                    for (int q = 0; q < N; q++) {
+                        xv[q] = O::add(xv[q], O::mul(alpha[s], pv[q]));
+                        pv[q] = O::add(O::mul(dv[q], rv[q]), O::mul(beta, pv[q]));
+                    }
+                    vstore<R>(xs + i * N, xv);
+                    vstore<R>(ps + i * N, pv);
+                }
+                if (blockIdx.x == 0)
+                    for (int64_t i = nvec * N + threadIdx.x; i < n; i += blockDim.x) {
+                        const R pi = ps[i];
+                        xs[i] = O::add(xs[i], O::mul(alpha[s], pi));
+                        ps[i] = O::add(O::mul(ds[i], rs[i]), O::mul(beta, pi));
+                    }
+            }
+        }
+        if (fin[0] || fin[1]) break;       // the kernel boundary is the barrier the survivor's next SpMV needs
+        grid_barrier(a.bar, bar_target);
+    }
+    // drain the prologue issued for an iteration that does not run here
+    {
+        int k = 0;
+        for (int tile = blockIdx.x; tile < num_tiles && k < STAGES; tile += gridDim.x, k++) {
+            const unsigned f = fills + (unsigned)k;
+            mbar_wait(&full[f % STAGES], (f / STAGES) & 1u);
+        }
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        for (int s = 0; s < 2; s++) {
+            CgState<R>* st = a.st + s;
+            st->rn2 = rr[s];
+            st->iter1 = it;
+            if (fin[s]) {
+                st->abs_new[it & 1] = abs_old[s];
+                st->iters = iters[s];
+                st->done = 1;
+            } else {
+                st->abs_new[0] = abs_old[s];  // pcg_persistent resumes from here
+            }
+        }
+    }
+}
+
+}  // namespace feab

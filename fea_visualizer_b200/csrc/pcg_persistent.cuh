@@ -186,7 +186,7 @@ __global__ void __launch_bounds__(ROWS, MINB) pcg_persistent(PcgArgs<R> a, Comm 
             if (d >= 0) reinterpret_cast<R*>(hp.base[hp.nb_rank[b]] + hp.off_vec[a.vec_p][hp.nb_rank[b]])[d] = val;
         }
     };
-    int it = 0, iters = 0;
+    int it = st->iter1, iters = 0;  // 0 after cg_begin; pcg_dual.cuh hands a running solve over with its count
     R rr = (R)0;
     const bool prof = a.prof != nullptr && blockIdx.x == 0 && threadIdx.x == 0;
     unsigned long long t_last = prof ? globaltimer_ns() : 0ull;

@@ -37,7 +37,7 @@ def test_library_exports_every_declared_symbol(lib):
 def test_struct_layouts_match_header():
     assert C.sizeof(feab.FeabParams) == 20
     assert C.sizeof(feab.FeabSolverOptions) == 32
-    assert C.sizeof(feab.FeabStats) == 2 * 8 + 2 * 8 + 8 + 8 + 8 + 8
+    assert C.sizeof(feab.FeabStats) == 2 * 8 + 2 * 8 + 8 + 8 + 8 + 8 + 8
 
 
 def test_no_gpu_means_error_not_fallback(lib):

@@ -217,6 +217,59 @@ def test_loop_modes_and_reruns_are_bitwise_identical(eq):
         assert (o[0] == outs[0][0]).all() and (o[1] == outs[0][1]).all() and o[2] == outs[0][2]
 
 
+
+# ---------------------------------------------------------------------------------------------- Gray-Scott dual-solve kernel
+@pytest.mark.parametrize("name,bc", [("ico8d", 0), ("disk14", 0), ("disk14", 1), ("grid", 1), ("ico24", 0)])
+def test_gray_scott_dual_solve_kernel(name, bc, monkeypatch):
+    """FEAB_DUAL=1: u- and v-solve of a step advance in lock-step in one persistent kernel (pcg_dual.cuh) and are handed over
+    to the single-system kernel when the first one stops.  Same recurrences: per-step parity vs the fp64 oracle <= 1e-8, the
+    iteration counts of both solves equal to the separate-solve path, fields equal to it to summation order, and
+    run-to-run identical bits."""
+    xyz, tri = meshes.icosphere(24) if name == "ico24" else cases()[name]
+    ob = meshes.boundary_flags(len(xyz), tri)
+    V = len(xyz)
+    D = O.Oracle(xyz, tri, ob, bc, real=64)
+    ref = []
+    run_steps(D, V, 3, 7, per_step=lambda s, X: ref.append((X.get_state(0), X.get_state(1))))
+    monkeypatch.setenv("FEAB_DUAL", "0")
+    S = make(64, xyz, tri, ob, bc, assembly=feab.ASSEMBLY_ORDERED)
+    sep = []
+    run_steps(S, V, 3, 7, per_step=lambda s, X: sep.append((X.get_state(0), X.get_state(1), tuple(X.stats()["iterations"][:2]))))
+    outs = []
+    for rep in range(2):
+        monkeypatch.setenv("FEAB_DUAL", "1")
+        F = make(64, xyz, tri, ob, bc, assembly=feab.ASSEMBLY_ORDERED)
+        got = []
+        run_steps(F, V, 3, 7, per_step=lambda s, X: got.append((X.get_state(0), X.get_state(1), tuple(X.stats()["iterations"][:2]))))
+        outs.append(got)
+        for s in range(7):
+            assert rel_l2(got[s][0], ref[s][0]) <= FP64_STEP_TOL and rel_l2(got[s][1], ref[s][1]) <= FP64_STEP_TOL, s
+            assert got[s][2] == sep[s][2], (s, got[s][2], sep[s][2])
+            assert rel_l2(got[s][0], sep[s][0]) <= 1e-12 and rel_l2(got[s][1], sep[s][1]) <= 1e-12, s
+        assert not F.unstable()
+        F.close()
+    for s in range(7):
+        assert (outs[0][s][0] == outs[1][s][0]).all() and (outs[0][s][1] == outs[1][s][1]).all()
+
+
+def test_gray_scott_dual_solve_zero_rhs_and_fp32(monkeypatch):
+    monkeypatch.setenv("FEAB_DUAL", "1")
+    xyz, tri = meshes.disk(7)
+    ob = meshes.boundary_flags(len(xyz), tri)
+    F = make(64, xyz, tri, ob, 0)
+    F.clear()
+    F.set_equation(3)
+    F.step(2)                      # v == 0: its right-hand side is zero, cg_begin settles it and the u-solve runs alone
+    assert (F.get_state(0) > 0).all() and (F.get_values() == 0).all() and F.stats()["iterations"][1] == 0
+    xyz, tri = meshes.icosphere(10)
+    ob = meshes.boundary_flags(len(xyz), tri)
+    G = make(32, xyz, tri, ob, 0)
+    monkeypatch.setenv("FEAB_DUAL", "0")
+    H = make(32, xyz, tri, ob, 0)
+    a, b = run_steps(G, len(xyz), 3, 6), run_steps(H, len(xyz), 3, 6)
+    assert rel_l2(a, b) <= 5e-6
+
+
 def test_multi_step_call_equals_single_steps_and_live_parameter_change():
     xyz, tri = meshes.icosphere(10)
     ob = meshes.boundary_flags(len(xyz), tri)
