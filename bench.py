@@ -326,7 +326,7 @@ def main():
     # algorithmic bytes of one Gray-Scott step: fused RHS + (it_u + it_v) PCG iterations
     it_bytes_row = nnz_all / n_all * (rb + 4) + 4 + 13 * rb
     # iterations the u- and the v-solve ran in lock-step (pcg_dual.cuh) read rowptr + columns once for both systems
-    shared = min(st.get("shared_iterations", 0), its[0], its[1]) if world == 1 else 0
+    shared = min(st.get("shared_iterations", 0), its[0], its[1])
     solve_bytes = (its[0] + its[1]) * it_bytes_row * n_all - shared * (4 * nnz_all + 4 * n_all)
     step_bytes = nnz_all * (rb + 4) + 4 * n_all + 8 * n_all * rb + solve_bytes
 

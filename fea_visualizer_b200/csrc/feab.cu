@@ -903,10 +903,10 @@ class SolverT final : public SolverBase {
 
     // PCG solve of slot `slot` into x.  capturing: build WHILE node into the graph being captured on stream_.
     bool dual_applies(bool capturing) const {
-        return dual_ && !capturing && opt_.loop_mode == FEAB_LOOP_PERSISTENT && eq_ == FEAB_EQ_REACTION_DIFFUSION && world_ == 1 && dual_max_grid_ > 0 &&
+        return dual_ && !capturing && opt_.loop_mode == FEAB_LOOP_PERSISTENT && eq_ == FEAB_EQ_REACTION_DIFFUSION && dual_max_grid_ > 0 &&
                !use_bicgstab();
     }
-    // Gray-Scott, one GPU: u- and v-solve advance together until the first of them stops (pcg_dual.cuh), then each is
+    // Gray-Scott: u- and v-solve advance together until the first of them stops (pcg_dual.cuh), then each is
     // finished (or found finished) by the single-system kernel, which resumes from CgState.
     void enqueue_dual(const R* const* A, const R* const* dinv, R* const* x) {
         cudaGraphConditionalHandle none = 0;
@@ -930,9 +930,10 @@ class SolverT final : public SolverBase {
         da.st = d_st_;
         da.part = d_dpart_.p;
         da.bar = d_bar_;
+        da.first_halo_tile = first_halo_tile(kDualRows);
         const int grid = std::min(dual_max_grid_, da.num_tiles);
         using DCfg = DualCfg<R, kDualRows, kPcgCpr, kPcgStages>;
-        void* kargs[] = {(void*)&da};
+        void* kargs[] = {(void*)&da, (void*)&cm_, (void*)&hp_};
         if (time_solves_) CK(cudaEventRecord(ev_solve_[0], stream_));
         CK(cudaLaunchCooperativeKernel((const void*)pcg_dual<R, kDualRows, kPcgCpr, kPcgStages, kPcgMinB>, dim3(grid), dim3(2 * kDualRows), kargs,
                                        DCfg::kSmemBytes, stream_));

@@ -9,8 +9,9 @@
 // (converged / maxit / non-finite), the kernel finishes the other one's iteration, stores its state and exits; the
 // single-system kernel (pcg_persistent.cuh) resumes it from CgState (abs_new[0], iter1).  Every operation on a system is
 // the one pcg_persistent performs; only the grouping of the per-CTA partial sums differs (256-row tiles), so results agree
-// with the other loop drivers to summation order, not bit for bit.  One GPU only (a partitioned handle runs the two solves
-// one after the other).
+// with the other loop drivers to summation order, not bit for bit.  On a partitioned handle the halo exchange and the
+// all-reduces are shared too: one flag value per iteration covers both directions, one mailbox round carries both p.Ap
+// (2 values) and one both |r|^2 and r.z (4 values).
 #pragma once
 #include "pcg_persistent.cuh"
 
@@ -31,6 +32,7 @@ struct PcgDualArgs {
     CgState<R>* st;           // [2], prepared by cg_begin
     R* part;                  // 6 x gridDim.x: pap0 | pap1 | rr0 | rr1 | rz0 | rz1
     unsigned long long* bar;  // zero at launch
+    int first_halo_tile;      // partitioned: first tile with a row that reads a ghost column
 };
 
 template <typename R, int ROWS, int CPR, int STAGES>
@@ -44,7 +46,7 @@ struct DualCfg {
 };
 
 template <typename R, int ROWS, int CPR, int STAGES, int MINB>
-__global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a) {
+__global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a, Comm cm, HaloPlan hp) {
     using Cfg = DualCfg<R, ROWS, CPR, STAGES>;
     using O = Ops<R>;
     constexpr int NWT = 2 * ROWS / 32;  // warps per CTA
@@ -53,6 +55,7 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a) {
     unsigned char* base = reinterpret_cast<unsigned char*>(((uintptr_t)smraw_dual + 127) & ~(uintptr_t)127);
     uint64_t* full = reinterpret_cast<uint64_t*>(base + Cfg::kStageBytes * STAGES);
     __shared__ R red[NWT + 1];
+    __shared__ double s_v[kMaxRanks * 4];
 
     if (a.st[0].done || a.st[1].done) return;  // cg_begin settled one of them: the single-system kernels take over (uniform)
     R thr[2] = {a.st[0].thr, a.st[1].thr};
@@ -100,6 +103,21 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a) {
     prologue();
 
     unsigned long long bar_target = 0;
+    unsigned long long ar_seq = 0, halo_seq = 0;
+    if (cm.world > 1) {
+        ar_seq = *(volatile unsigned long long*)&cm.loc->ar_seq;
+        halo_seq = *(volatile unsigned long long*)&cm.loc->halo_seq;
+    }
+    // partitioned solve: mirror a boundary row's new p_s on every neighbour that keeps it as a ghost
+    auto push_row = [&](int sys, int64_t row, R val) {
+        if (row < hp.n_int) return;
+        const int* tb = hp.push_tab + (size_t)(row - hp.n_int) * hp.nnb;
+        const int vec = sys == 0 ? kVecP0 : kVecP1;
+        for (int b = 0; b < hp.nnb; b++) {
+            const int d = tb[b];
+            if (d >= 0) reinterpret_cast<R*>(hp.base[hp.nb_rank[b]] + hp.off_vec[vec][hp.nb_rank[b]])[d] = val;
+        }
+    };
     const int G = (int)gridDim.x;
     R* const part = a.part;
     constexpr int N = Vec<R>::N;
@@ -117,8 +135,14 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a) {
     while (true) {
         // ---------------- phase A: y_s = A_s p_s for both systems from one staged index stream ----------------
         R acc = (R)0;
+        bool halo_ok = cm.world == 1;
         int k = 0;
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, k++) {
+            if (!halo_ok && tile >= a.first_halo_tile) {  // both directions' ghosts arrive under one flag value
+                if (threadIdx.x == 0) wait_flags(cm, hp, 0, halo_seq);
+                __syncthreads();
+                halo_ok = true;
+            }
             const unsigned f = fills + (unsigned)k;
             const int s = (int)(f % STAGES);
             mbar_wait(&full[s], (f / STAGES) & 1u);
@@ -206,6 +230,7 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a) {
         R pap[2];
         pap[0] = sum_cta_partials<R, NWT>(part, red);
         pap[1] = sum_cta_partials<R, NWT>(part + G, red);
+        if (cm.world > 1) ar_exchange<R, 2>(cm, ar_seq, pap, s_v);
 
         // ---------------- phase B (both systems): r -= alpha y, |r|^2, r.z ----------------
         R alpha[2];
@@ -250,11 +275,20 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a) {
         }
         grid_barrier(a.bar, bar_target);
         R rz[2];
+        {
+            R t4[4];
 #pragma unroll
-        for (int s = 0; s < 2; s++) {
-            rr[s] = sum_cta_partials<R, NWT>(part + (size_t)(2 + s) * G, red);
-            rz[s] = sum_cta_partials<R, NWT>(part + (size_t)(4 + s) * G, red);
+            for (int s = 0; s < 2; s++) {
+                t4[s] = sum_cta_partials<R, NWT>(part + (size_t)(2 + s) * G, red);
+                t4[2 + s] = sum_cta_partials<R, NWT>(part + (size_t)(4 + s) * G, red);
+            }
+            if (cm.world > 1) ar_exchange<R, 4>(cm, ar_seq, t4, s_v);
+            rr[0] = t4[0];
+            rr[1] = t4[1];
+            rz[0] = t4[2];
+            rz[1] = t4[3];
         }
+        bool pushed = false;
         // ---------------- stopping tests (ConjugateGradient.h:72-73), per system; direction update for the ones that go on ----
 #pragma unroll
         for (int s = 0; s < 2; s++) {
@@ -293,17 +327,41 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a) {
                     }
                     vstore<R>(xs + i * N, xv);
                     vstore<R>(ps + i * N, pv);
+                    if (cm.world > 1 && i * N + N > hp.n_int) {  // boundary rows: straight into the neighbours' ghost tails
+#pragma unroll
+                        for (int q = 0; q < N; q++) push_row(s, i * N + q, pv[q]);
+                        pushed = true;
+                    }
                 }
                 if (blockIdx.x == 0)
                     for (int64_t i = nvec * N + threadIdx.x; i < n; i += blockDim.x) {
                         const R pi = ps[i];
                         xs[i] = O::add(xs[i], O::mul(alpha[s], pi));
-                        ps[i] = O::add(O::mul(ds[i], rs[i]), O::mul(beta, pi));
+                        const R pn = O::add(O::mul(ds[i], rs[i]), O::mul(beta, pi));
+                        ps[i] = pn;
+                        if (cm.world > 1) {
+                            push_row(s, i, pn);
+                            pushed = true;
+                        }
                     }
             }
         }
-        if (fin[0] || fin[1]) break;       // the kernel boundary is the barrier the survivor's next SpMV needs
-        grid_barrier(a.bar, bar_target);
+        if (fin[0] && fin[1]) break;
+        if (cm.world == 1) {
+            if (fin[0] || fin[1]) break;  // the kernel boundary is the barrier the survivor's next SpMV needs
+            grid_barrier(a.bar, bar_target);
+        } else {
+            // same hand-shake as pcg_persistent.cuh: pushers fence, grid barrier, then one flag value covers both directions.
+            // A survivor's last push here is what its first SpMV in the single-system kernel waits for.
+            if (__syncthreads_or(pushed ? 1 : 0)) __threadfence_system();
+            grid_barrier(a.bar, bar_target);
+            halo_seq += 1;
+            if (blockIdx.x == 0) {
+                if (threadIdx.x == 0) cm.loc->halo_seq = halo_seq;
+                if ((int)threadIdx.x < hp.nnb) st_relaxed_sys(&cm.ctrl[hp.nb_rank[threadIdx.x]]->halo_flag[cm.rank], halo_seq);
+            }
+            if (fin[0] || fin[1]) break;
+        }
     }
     // drain the prologue issued for an iteration that does not run here
     {

@@ -85,7 +85,7 @@ typedef struct {
     int64_t last_call_steps;
     int64_t kernel_launches;   /* kernels launched by this handle since creation (graph nodes counted per execution) */
     double solve_ms;           /* PERSISTENT loop: device time of the PCG kernel(s) of the LAST step of the last call; else 0 */
-    int64_t shared_iterations; /* Gray-Scott on one GPU: SpMV passes of the last step in which the u- and the v-solve ran in lock-step
+    int64_t shared_iterations; /* Gray-Scott: SpMV passes of the last step in which the u- and the v-solve ran in lock-step
                                   from one index stream (pcg_dual.cuh); 0 when the two solves ran one after the other */
 } FeabStats;
 

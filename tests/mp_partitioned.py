@@ -3,7 +3,7 @@
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P tests/mp_partitioned.py
 
 Every rank owns one GPU and one partition of the same mesh; halos and all-reduces travel through cudaIpc-mapped peer
-memory inside the solver kernels (csrc/comm.cuh).  Checked on every rank, for all four equations, in both loop modes:
+memory inside the solver kernels (csrc/comm.cuh).  Checked on every rank, for all four equations, with all three loop drivers (the persistent one runs Gray-Scott through pcg_dual):
   * the fields after each of 5 steps against the fp64 oracle (<= 1e-8 relative L2, the north star's per-step bar),
   * surface->values complete and identical on every rank after a synchronising step (the reference's data contract),
   * FEAB_SYNC_ROOT: values in and out through rank 0's host array only,
@@ -48,7 +48,7 @@ def main():
         V = len(xyz)
         seeds = meshes.seed_nodes(V)
         D = O.Oracle(xyz, tri, ob, bc, real=64)
-        for loop in (feab.LOOP_GRAPH_WHILE, feab.LOOP_HOST_BATCHED):
+        for loop in (feab.LOOP_GRAPH_WHILE, feab.LOOP_HOST_BATCHED, feab.LOOP_PERSISTENT):
             F = feab.Feab(real=64, device=local)
             F.mg_config(rank, world)
             F.set_boundary_condition(bc)
@@ -102,6 +102,8 @@ def main():
                 assert e <= 2e-8, (name, bc, loop, eq, "multi-step call", e)
             st = F.stats()
             assert st["kernel_launches"] > 0
+            if loop == feab.LOOP_PERSISTENT:      # the last equation was Gray-Scott: both solves shared the dual kernel
+                assert st["shared_iterations"] > 0, st
             dist.barrier()
             F.close()
     dist.barrier()
