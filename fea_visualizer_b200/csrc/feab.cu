@@ -185,7 +185,8 @@ class SolverT final : public SolverBase {
         CK(cudaMalloc(&d_bar_, 4 * sizeof(unsigned long long)));
         CK(cudaMemset(d_bar_, 0, 4 * sizeof(unsigned long long)));
         for (int i = 0; i < 4; i++) CK(cudaEventCreate(&ev_solve_[i]));
-        if (getenv("FEAB_PCG_PROF")) {
+        if (const char* v = getenv("FEAB_PCG_PROF")) {  // 1: stamps of pcg_persistent, 2: stamps of pcg_dual
+            prof_dual_ = atoi(v) == 2;
             CK(cudaMalloc(&d_prof_, 16 * sizeof(unsigned long long)));
             CK(cudaMemset(d_prof_, 0, 16 * sizeof(unsigned long long)));
         }
@@ -931,6 +932,7 @@ class SolverT final : public SolverBase {
         da.part = d_dpart_.p;
         da.bar = d_bar_;
         da.first_halo_tile = first_halo_tile(kDualRows);
+        da.prof = prof_dual_ ? d_prof_ : nullptr;
         const int grid = std::min(dual_max_grid_, da.num_tiles);
         using DCfg = DualCfg<R, kDualRows, kPcgCpr, kPcgStages>;
         void* kargs[] = {(void*)&da, (void*)&cm_, (void*)&hp_};
@@ -965,7 +967,7 @@ class SolverT final : public SolverBase {
             pa.part = d_ppart_.p;
             pa.bar = d_bar_ + 2 * slot;
             pa.vec_p = slot == 0 ? kVecP0 : kVecP1;
-            pa.prof = d_prof_;
+            pa.prof = prof_dual_ ? nullptr : d_prof_;
             const int grid = std::min(pcg_max_grid_, pa.num_tiles);
             using PCfg = TmaCfg<R, kPcgRows, kPcgCpr, kPcgStages>;
             void* kargs[] = {(void*)&pa, (void*)&cm_, (void*)&hp_};
@@ -1486,6 +1488,7 @@ class SolverT final : public SolverBase {
     DevBuf<R> d_dpart_;
     bool rhs_tma_ = true;
     unsigned long long* d_bar_ = nullptr;
+    bool prof_dual_ = false;
     unsigned long long* d_prof_ = nullptr;  // FEAB_PCG_PROF=1: phase timers of the persistent kernel (CTA 0)
     DevBuf<R> d_ppart_;
     cudaEvent_t ev_solve_[4] = {};

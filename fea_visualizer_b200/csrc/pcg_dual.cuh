@@ -33,6 +33,7 @@ struct PcgDualArgs {
     R* part;                  // 6 x gridDim.x: pap0 | pap1 | rr0 | rr1 | rz0 | rz1
     unsigned long long* bar;  // zero at launch
     int first_halo_tile;      // partitioned: first tile with a row that reads a ghost column
+    unsigned long long* prof; // optional (FEAB_PCG_PROF=2): ns spent by CTA 0, same slots as PcgArgs::prof
 };
 
 template <typename R, int ROWS, int CPR, int STAGES>
@@ -129,9 +130,18 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a, Com
     R* const yh = a.y[h];
 
     int it = a.st[0].iter1;
+    const int it0 = it;
     int iters[2] = {0, 0};
     bool fin[2] = {false, false};
     R rr[2] = {(R)0, (R)0};
+    const bool prof = a.prof != nullptr && blockIdx.x == 0 && threadIdx.x == 0;
+    unsigned long long t_last = prof ? globaltimer_ns() : 0ull;
+#define DUAL_STAMP(slot)                                   \
+    if (prof) {                                            \
+        const unsigned long long t_now = globaltimer_ns(); \
+        a.prof[slot] += t_now - t_last;                    \
+        t_last = t_now;                                    \
+    }
     while (true) {
         // ---------------- phase A: y_s = A_s p_s for both systems from one staged index stream ----------------
         R acc = (R)0;
@@ -226,11 +236,14 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a, Com
         }
         __syncthreads();
         prologue();
+        DUAL_STAMP(0)
         grid_barrier(a.bar, bar_target);
         R pap[2];
         pap[0] = sum_cta_partials<R, NWT>(part, red);
         pap[1] = sum_cta_partials<R, NWT>(part + G, red);
+        DUAL_STAMP(1)
         if (cm.world > 1) ar_exchange<R, 2>(cm, ar_seq, pap, s_v);
+        DUAL_STAMP(2)
 
         // ---------------- phase B (both systems): r -= alpha y, |r|^2, r.z ----------------
         R alpha[2];
@@ -273,6 +286,7 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a, Com
                 part[(size_t)(4 + s) * G + blockIdx.x] = prz;
             }
         }
+        DUAL_STAMP(3)
         grid_barrier(a.bar, bar_target);
         R rz[2];
         {
@@ -282,7 +296,9 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a, Com
                 t4[s] = sum_cta_partials<R, NWT>(part + (size_t)(2 + s) * G, red);
                 t4[2 + s] = sum_cta_partials<R, NWT>(part + (size_t)(4 + s) * G, red);
             }
+            DUAL_STAMP(4)
             if (cm.world > 1) ar_exchange<R, 4>(cm, ar_seq, t4, s_v);
+            DUAL_STAMP(5)
             rr[0] = t4[0];
             rr[1] = t4[1];
             rz[0] = t4[2];
@@ -346,23 +362,29 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a, Com
                     }
             }
         }
+        DUAL_STAMP(6)
         if (fin[0] && fin[1]) break;
         if (cm.world == 1) {
             if (fin[0] || fin[1]) break;  // the kernel boundary is the barrier the survivor's next SpMV needs
             grid_barrier(a.bar, bar_target);
+            DUAL_STAMP(7)
         } else {
             // same hand-shake as pcg_persistent.cuh: pushers fence, grid barrier, then one flag value covers both directions.
             // A survivor's last push here is what its first SpMV in the single-system kernel waits for.
             if (__syncthreads_or(pushed ? 1 : 0)) __threadfence_system();
             grid_barrier(a.bar, bar_target);
+            DUAL_STAMP(7)
             halo_seq += 1;
             if (blockIdx.x == 0) {
                 if (threadIdx.x == 0) cm.loc->halo_seq = halo_seq;
                 if ((int)threadIdx.x < hp.nnb) st_relaxed_sys(&cm.ctrl[hp.nb_rank[threadIdx.x]]->halo_flag[cm.rank], halo_seq);
             }
+            DUAL_STAMP(8)
             if (fin[0] || fin[1]) break;
         }
     }
+#undef DUAL_STAMP
+    if (prof) a.prof[9] += (unsigned long long)(it - it0);
     // drain the prologue issued for an iteration that does not run here
     {
         int k = 0;

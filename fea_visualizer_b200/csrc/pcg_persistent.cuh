@@ -187,6 +187,7 @@ __global__ void __launch_bounds__(ROWS, MINB) pcg_persistent(PcgArgs<R> a, Comm 
         }
     };
     int it = st->iter1, iters = 0;  // 0 after cg_begin; pcg_dual.cuh hands a running solve over with its count
+    const int it0 = it;
     R rr = (R)0;
     const bool prof = a.prof != nullptr && blockIdx.x == 0 && threadIdx.x == 0;
     unsigned long long t_last = prof ? globaltimer_ns() : 0ull;
@@ -406,7 +407,7 @@ __global__ void __launch_bounds__(ROWS, MINB) pcg_persistent(PcgArgs<R> a, Comm 
         PCG_STAMP(8)
     }
 #undef PCG_STAMP
-    if (prof) a.prof[9] += (unsigned long long)it;
+    if (prof) a.prof[9] += (unsigned long long)(it - it0);
     // drain the prologue issued for an iteration that never runs, so no bulk copy is in flight at exit
     {
         int k = 0;
