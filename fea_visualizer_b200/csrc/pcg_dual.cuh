@@ -257,7 +257,7 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a, Com
             for (int64_t i = gtid; i < nvec; i += gthreads) {
                 R rv[N], yv[N], dv[N];
                 vload<R>(rs + i * N, rv);
-                vload<R>(ys + i * N, yv);
+                vload_cs<R>(ys + i * N, yv);
                 vload<R>(ds + i * N, dv);
 #pragma unroll
                 for (int q = 0; q < N; q++) {
@@ -317,11 +317,11 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a, Com
                 if (!conv) abs_old[s] = rz[s];
                 for (int64_t i = gtid; i < nvec; i += gthreads) {  // the deferred x += alpha p of the last iteration
                     R xv[N], pv[N];
-                    vload<R>(xs + i * N, xv);
+                    vload_cs<R>(xs + i * N, xv);
                     vload<R>(ps + i * N, pv);
 #pragma unroll
                     for (int q = 0; q < N; q++) xv[q] = O::add(xv[q], O::mul(alpha[s], pv[q]));
-                    vstore<R>(xs + i * N, xv);
+                    vstore_cs<R>(xs + i * N, xv);
                 }
                 if (blockIdx.x == 0)
                     for (int64_t i = nvec * N + threadIdx.x; i < n; i += blockDim.x) xs[i] = O::add(xs[i], O::mul(alpha[s], ps[i]));
@@ -332,7 +332,7 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a, Com
                 const R* const ds = a.dinv[s];
                 for (int64_t i = gtid; i < nvec; i += gthreads) {
                     R xv[N], rv[N], pv[N], dv[N];
-                    vload<R>(xs + i * N, xv);
+                    vload_cs<R>(xs + i * N, xv);
                     vload<R>(rs + i * N, rv);
                     vload<R>(ps + i * N, pv);
                     vload<R>(ds + i * N, dv);
@@ -341,7 +341,7 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a, Com
                         xv[q] = O::add(xv[q], O::mul(alpha[s], pv[q]));
                         pv[q] = O::add(O::mul(dv[q], rv[q]), O::mul(beta, pv[q]));
                     }
-                    vstore<R>(xs + i * N, xv);
+                    vstore_cs<R>(xs + i * N, xv);
                     vstore<R>(ps + i * N, pv);
                     if (cm.world > 1 && i * N + N > hp.n_int) {  // boundary rows: straight into the neighbours' ghost tails
 #pragma unroll

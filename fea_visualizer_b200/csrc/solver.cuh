@@ -237,6 +237,34 @@ __device__ __forceinline__ void vstore<float>(float* p, const float* in) {
     *reinterpret_cast<float4*>(p) = make_float4(in[0], in[1], in[2], in[3]);
 }
 
+// Streaming ("evict first") variants for data touched once per iteration, so that it does not push re-used vectors out of L2.
+template <typename R>
+__device__ __forceinline__ void vload_cs(const R* p, R* out);
+template <>
+__device__ __forceinline__ void vload_cs<double>(const double* p, double* out) {
+    double2 v = __ldcs(reinterpret_cast<const double2*>(p));
+    out[0] = v.x;
+    out[1] = v.y;
+}
+template <>
+__device__ __forceinline__ void vload_cs<float>(const float* p, float* out) {
+    float4 v = __ldcs(reinterpret_cast<const float4*>(p));
+    out[0] = v.x;
+    out[1] = v.y;
+    out[2] = v.z;
+    out[3] = v.w;
+}
+template <typename R>
+__device__ __forceinline__ void vstore_cs(R* p, const R* in);
+template <>
+__device__ __forceinline__ void vstore_cs<double>(double* p, const double* in) {
+    __stcs(reinterpret_cast<double2*>(p), make_double2(in[0], in[1]));
+}
+template <>
+__device__ __forceinline__ void vstore_cs<float>(float* p, const float* in) {
+    __stcs(reinterpret_cast<float4*>(p), make_float4(in[0], in[1], in[2], in[3]));
+}
+
 template <typename R>
 __global__ void __launch_bounds__(kBlock) cg_update(R* __restrict__ x, R* __restrict__ r, const R* __restrict__ p,
                                                     const R* __restrict__ y, const R* __restrict__ dinv, int64_t n,
