@@ -1116,6 +1116,7 @@ class SolverT final : public SolverBase {
             // BiCGSTAB has no persistent kernel: it keeps the WHILE graph unless host batching was asked for
             const bool graph_mode = opt_.loop_mode == FEAB_LOOP_GRAPH_WHILE || (opt_.loop_mode == FEAB_LOOP_PERSISTENT && use_bicgstab());
             graph_mode_last_ = graph_mode;
+            if (graph_mode) dual_last_ = false;  // a graph replays separate solves
             if (graph_mode && (!graph_exec_ || graph_eq_ != eq_)) build_graph();
             for (int s = 0; s < nsteps; s++) {
                 time_solves_ = !graph_mode && opt_.loop_mode == FEAB_LOOP_PERSISTENT && s == nsteps - 1;

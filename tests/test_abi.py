@@ -34,6 +34,19 @@ def test_library_exports_every_declared_symbol(lib):
         assert hasattr(lib, name), name
 
 
+def header_struct_fields(name):
+    """Field names of `typedef struct { ... } <name>;` in include/feab.h, in declaration order."""
+    text = open(os.path.join(ROOT, "include", "feab.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    body = re.search(r"typedef struct\s*\{([^}]*)\}\s*" + name + r"\s*;", text).group(1)
+    return [re.sub(r"\[.*?\]", "", d.split()[-1]) for d in body.split(";") if d.strip()]
+
+
+def test_struct_fields_follow_the_header_order():
+    for ct in (feab.FeabParams, feab.FeabSolverOptions, feab.FeabStats):
+        assert header_struct_fields(ct.__name__) == [f[0] for f in ct._fields_], ct.__name__
+
+
 def test_struct_layouts_match_header():
     assert C.sizeof(feab.FeabParams) == 20
     assert C.sizeof(feab.FeabSolverOptions) == 32
