@@ -50,6 +50,19 @@ def ncu_traffic(rows, dtype):
     return None
 
 
+def ncu_solve_traffic(rows, dtype, its, shared):
+    """DRAM bytes per step of the persistent PCG kernels (pcg_dual + the pcg_persistent tail) from the committed ncu captures of
+    the same workload (profiles/r01_v7_solve_traffic.json); None when workload or iteration counts differ."""
+    p = os.path.join(ROOT, "profiles", "r01_v7_solve_traffic.json")
+    try:
+        t = json.load(open(p))
+        if t["rows"] == rows and t["dtype"] == dtype and list(t["iterations"]) == list(its) and t["shared_iterations"] == shared:
+            return t["traffic_bytes_per_step"]
+    except Exception:
+        pass
+    return None
+
+
 def measured_peak():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -341,9 +354,26 @@ def main():
         k0 = kernels["spmv_dot"]
         it_ms = kernels["spmv_dot"]["ms"] + kernels["cg_update"]["ms"] + kernels["cg_direction"]["ms"]
         it_bytes = sum(kernels[k]["algorithmic_bytes"] for k in ("spmv_dot", "cg_update", "cg_direction"))
-        roof = {"bound": "hbm", "kernel": "spmv_dot", "achieved": k0["GBps"], "peak": peak, "unit": "GB/s", "frac": k0["GBps"] / peak,
-                "traffic": ncu_traffic(n, "f64" if args.real == 64 else "f32"), "algorithmic_bytes": k0["algorithmic_bytes"],
-                "traffic_source": "profiles/r01_spmv_traffic.json (ncu --set full, per launch)", "peak_source": peak_src, "frac_of_nominal_8TBps": k0["GBps"] / 8000.0,
+        dt_name = "f64" if args.real == 64 else "f32"
+        spmv_alone = {"kernel": "spmv_dot (the standalone SpMV + dot kernel, timed alone; the persistent kernels run the same tile loop)",
+                      "achieved": k0["GBps"], "frac": k0["GBps"] / peak, "frac_of_nominal_8TBps": k0["GBps"] / 8000.0,
+                      "algorithmic_bytes": k0["algorithmic_bytes"], "traffic": ncu_traffic(n, dt_name),
+                      "traffic_source": "profiles/r01_spmv_traffic.json (ncu --set full, per launch)"}
+        if solve_ms:
+            # the dominant kernels of the timed region: the persistent PCG solves (pcg_dual for the lock-step passes, pcg_persistent
+            # for the longer solve's tail; pcg_persistent alone with FEAB_DUAL=0), events on the solver stream around the last step's
+            head = {"kernel": "persistent PCG solve kernels of one step (pcg_dual + pcg_persistent tail)" if shared else
+                    "persistent PCG solve kernels of one step (pcg_persistent x 2)",
+                    "achieved": solve_bytes / solve_ms / 1e6, "algorithmic_bytes": solve_bytes, "ms": solve_ms,
+                    "traffic": ncu_solve_traffic(n, dt_name, its, shared),
+                    "traffic_source": "profiles/r01_v7_solve_traffic.json (ncu, per step)"}
+        else:
+            head = {"kernel": "spmv_dot", "achieved": k0["GBps"], "algorithmic_bytes": k0["algorithmic_bytes"], "ms": k0["ms"],
+                    "traffic": spmv_alone["traffic"], "traffic_source": spmv_alone["traffic_source"]}
+        roof = {"bound": "hbm", "kernel": head["kernel"], "achieved": head["achieved"], "peak": peak, "unit": "GB/s", "frac": head["achieved"] / peak,
+                "traffic": head["traffic"], "algorithmic_bytes": head["algorithmic_bytes"], "ms_per_launch_group": head["ms"],
+                "traffic_source": head["traffic_source"], "peak_source": peak_src, "frac_of_nominal_8TBps": head["achieved"] / 8000.0,
+                "spmv_dot_alone": spmv_alone,
                 "pcg_iteration": {"ms": it_ms, "algorithmic_bytes": it_bytes, "GBps": it_bytes / it_ms / 1e6,
                                   "frac": it_bytes / it_ms / 1e6 / peak},
                 "pcg_persistent_last_step": None if not solve_ms else {

@@ -246,8 +246,9 @@ def test_gray_scott_dual_solve_kernel(name, bc, monkeypatch):
             assert rel_l2(got[s][0], ref[s][0]) <= FP64_STEP_TOL and rel_l2(got[s][1], ref[s][1]) <= FP64_STEP_TOL, s
             assert got[s][2] == sep[s][2], (s, got[s][2], sep[s][2])
             assert rel_l2(got[s][0], sep[s][0]) <= 1e-12 and rel_l2(got[s][1], sep[s][1]) <= 1e-12, s
-        assert not F.unstable()
+        assert not F.unstable() and F.stats()["shared_iterations"] > 0
         F.close()
+    assert S.stats()["shared_iterations"] == 0
     for s in range(7):
         assert (outs[0][s][0] == outs[1][s][0]).all() and (outs[0][s][1] == outs[1][s][1]).all()
 
