@@ -96,6 +96,31 @@ __device__ __forceinline__ T block_sum_n(T v, T* sm /* NW + 1 */) {
     return sm[NW];
 }
 
+// K sums at once, each added in exactly the order block_sum_n uses (so the bits are the same), with two CTA barriers
+// instead of 2 K (+ one trailing barrier so that `sm` can be reused at once).  `sm` must hold (NW + 1) * K elements.
+template <typename T, int K, int NW>
+__device__ __forceinline__ void block_sum_vec(T (&v)[K], T* sm) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+    for (int k = 0; k < K; k++) {
+        v[k] = warp_sum(v[k]);
+        if (lane == 0) sm[w * K + k] = v[k];
+    }
+    __syncthreads();
+    if (w == 0) {
+#pragma unroll
+        for (int k = 0; k < K; k++) {
+            T t = lane < NW ? sm[lane * K + k] : T(0);
+            t = warp_sum(t);
+            if (lane == 0) sm[NW * K + k] = t;
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < K; k++) v[k] = sm[NW * K + k];
+    __syncthreads();
+}
+
 // Deterministic grid-wide sum of `count` per-CTA partials, computed redundantly (and identically) by every
 // CTA of the consuming kernel: no atomics, no "last block" fence, no host round trip.
 template <typename T>

@@ -5,7 +5,7 @@
 //   * one index stream (rowptr + columns, 32 B/row) feeds both SpMVs: a 256-row tile is staged once together with BOTH value
 //     streams; threads 0..255 of the CTA multiply system 0, threads 256..511 system 1;
 //   * the three grid barriers of an iteration are shared.
-// Per shared iteration this moves 336 instead of 368 B/row and pays 3 instead of 6 barriers.  As soon as one system stops
+// Per shared iteration this moves 336 instead of 384 B/row and pays 3 instead of 6 barriers.  As soon as one system stops
 // (converged / maxit / non-finite), the kernel finishes the other one's iteration, stores its state and exits; the
 // single-system kernel (pcg_persistent.cuh) resumes it from CgState (abs_new[0], iter1).  Every operation on a system is
 // the one pcg_persistent performs; only the grouping of the per-CTA partial sums differs (256-row tiles), so results agree
@@ -55,7 +55,7 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a, Com
     extern __shared__ unsigned char smraw_dual[];
     unsigned char* base = reinterpret_cast<unsigned char*>(((uintptr_t)smraw_dual + 127) & ~(uintptr_t)127);
     uint64_t* full = reinterpret_cast<uint64_t*>(base + Cfg::kStageBytes * STAGES);
-    __shared__ R red[NWT + 1];
+    __shared__ R red[(NWT + 1) * 4];
     __shared__ double s_v[kMaxRanks * 4];
 
     if (a.st[0].done || a.st[1].done) return;  // cg_begin settled one of them: the single-system kernels take over (uniform)
@@ -239,14 +239,14 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a, Com
         DUAL_STAMP(0)
         grid_barrier(a.bar, bar_target);
         R pap[2];
-        pap[0] = sum_cta_partials<R, NWT>(part, red);
-        pap[1] = sum_cta_partials<R, NWT>(part + G, red);
+        sum_cta_partials_vec<R, 2, NWT>(part, (size_t)G, pap, red);
         DUAL_STAMP(1)
         if (cm.world > 1) ar_exchange<R, 2>(cm, ar_seq, pap, s_v);
         DUAL_STAMP(2)
 
         // ---------------- phase B (both systems): r -= alpha y, |r|^2, r.z ----------------
         R alpha[2];
+        R pb[4];  // |r_0|^2, |r_1|^2, r_0.z_0, r_1.z_1 of this CTA
 #pragma unroll
         for (int s = 0; s < 2; s++) {
             alpha[s] = abs_old[s] / pap[s];
@@ -277,25 +277,20 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a, Com
                     prz += rn * z;
                 }
             }
-            prr = block_sum_n<R, NWT>(prr, red);
-            __syncthreads();
-            prz = block_sum_n<R, NWT>(prz, red);
-            __syncthreads();
-            if (threadIdx.x == 0) {
-                part[(size_t)(2 + s) * G + blockIdx.x] = prr;
-                part[(size_t)(4 + s) * G + blockIdx.x] = prz;
-            }
+            pb[s] = prr;
+            pb[2 + s] = prz;
+        }
+        block_sum_vec<R, 4, NWT>(pb, red);
+        if (threadIdx.x == 0) {
+#pragma unroll
+            for (int k = 0; k < 4; k++) part[(size_t)(2 + k) * G + blockIdx.x] = pb[k];
         }
         DUAL_STAMP(3)
         grid_barrier(a.bar, bar_target);
         R rz[2];
         {
             R t4[4];
-#pragma unroll
-            for (int s = 0; s < 2; s++) {
-                t4[s] = sum_cta_partials<R, NWT>(part + (size_t)(2 + s) * G, red);
-                t4[2 + s] = sum_cta_partials<R, NWT>(part + (size_t)(4 + s) * G, red);
-            }
+            sum_cta_partials_vec<R, 4, NWT>(part + (size_t)2 * G, (size_t)G, t4, red);
             DUAL_STAMP(4)
             if (cm.world > 1) ar_exchange<R, 4>(cm, ar_seq, t4, s_v);
             DUAL_STAMP(5)

@@ -71,6 +71,18 @@ __device__ __forceinline__ R sum_cta_partials(const R* part, R* red) {
     return s;
 }
 
+// K such sums at once (partials of sum k at part + k * stride): one pass over L2, one block reduction; same bits.
+template <typename R, int K, int NW>
+__device__ __forceinline__ void sum_cta_partials_vec(const R* part, size_t stride, R (&out)[K], R* red /* (NW + 1) * K */) {
+#pragma unroll
+    for (int k = 0; k < K; k++) out[k] = (R)0;
+    for (int i = threadIdx.x; i < (int)gridDim.x; i += blockDim.x) {
+#pragma unroll
+        for (int k = 0; k < K; k++) out[k] += __ldcg(part + k * stride + i);
+    }
+    block_sum_vec<R, K, NW>(out, red);
+}
+
 // Mailbox all-reduce riding on a grid barrier: CTA 0 stores the rank totals into every peer's mailbox (one thread per
 // peer, LL words: no fence), every CTA waits for the peers' totals in its own mailbox (one thread per peer) and adds
 // them in rank order -- bit-identical on all CTAs of all ranks.
@@ -112,7 +124,7 @@ __global__ void __launch_bounds__(ROWS, MINB) pcg_persistent(PcgArgs<R> a, Comm 
     extern __shared__ unsigned char smraw_pcg[];
     unsigned char* base = reinterpret_cast<unsigned char*>(((uintptr_t)smraw_pcg + 127) & ~(uintptr_t)127);
     uint64_t* full = reinterpret_cast<uint64_t*>(base + Cfg::kStageBytes * STAGES);
-    __shared__ R red[NW + 1];
+    __shared__ R red[(NW + 1) * 2];
     __shared__ double s_v[kMaxRanks * 4];
 
     CgState<R>* st = a.st;
@@ -319,18 +331,18 @@ __global__ void __launch_bounds__(ROWS, MINB) pcg_persistent(PcgArgs<R> a, Comm 
                 prz += rn * z;
             }
         }
-        prr = block_sum_n<R, NW>(prr, red);
-        __syncthreads();
-        prz = block_sum_n<R, NW>(prz, red);
-        if (threadIdx.x == 0) {
-            part_rr[blockIdx.x] = prr;
-            part_rz[blockIdx.x] = prz;
+        {
+            R pr2[2] = {prr, prz};
+            block_sum_vec<R, 2, NW>(pr2, red);
+            if (threadIdx.x == 0) {
+                part_rr[blockIdx.x] = pr2[0];
+                part_rz[blockIdx.x] = pr2[1];
+            }
         }
         PCG_STAMP(3)
         grid_barrier(a.bar, bar_target);
         R t2[2];
-        t2[0] = sum_cta_partials<R, NW>(part_rr, red);
-        t2[1] = sum_cta_partials<R, NW>(part_rz, red);
+        sum_cta_partials_vec<R, 2, NW>(part_rr, (size_t)gridDim.x, t2, red);  // part_rz = part_rr + gridDim.x
         PCG_STAMP(4)
         if (cm.world > 1) ar_exchange<R, 2>(cm, ar_seq, t2, s_v);
         PCG_STAMP(5)
