@@ -12,6 +12,8 @@
 // with the other loop drivers to summation order, not bit for bit.  On a partitioned handle the halo exchange and the
 // all-reduces are shared too: one flag value per iteration covers both directions, one mailbox round carries both p.Ap
 // (2 values) and one both |r|^2 and r.z (4 values).
+// x (phase C only) and the phase-B read of y are streaming accesses (ld/st.cs): touched once per iteration, they should
+// not push r, p, dinv of two systems out of L2.  The 2 + 4 + 4 sums of an iteration are reduced as vectors (common.cuh).
 #pragma once
 #include "pcg_persistent.cuh"
 
