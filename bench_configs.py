@@ -45,6 +45,21 @@ def drive(X, V, eq, nsteps, seeds):
         X.step(1)
 
 
+def pslg_disk(radius=57.3, sides=4096, area=0.004):
+    """SURVEY.md 8(d) C4: a regular 4096-gon through the reference's own PSLG hand-off (Surface::init_from_PSLG ->
+    Triangle "Qeqpza<area>", src/Utils/Surface.cpp:25-51, :431-486) when the compiled reference travelled with the snapshot
+    (oracle/_ref/libfea_surface_ref.so; mesh generation is input preparation, not the measured path).  area = 0.004 prints in
+    fixed notation, so the reference's std::format string is parsed by Triangle as intended.  ~4.0 M triangles."""
+    from oracle import surface_oracle as S
+    if not S.available():
+        return None
+    th = np.linspace(0, 2 * np.pi, sides, endpoint=False)
+    R = S.RefSurface()
+    R.init_from_pslg(np.stack([radius * np.cos(th), radius * np.sin(th)], 1), area)
+    xyz, _, tri, ob = R.get_mesh()
+    return xyz, tri, ob
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--only", default="")
@@ -65,15 +80,20 @@ def main():
     # C4: advection-diffusion on a ~4 M-triangle disk, Dirichlet; reference-parity mode (PCG on A^T) and BiCGSTAB
     configs.append(("C4", "disk, 816 rings (~4.0 M triangles)", lambda: meshes.disk(816), 2, 20, 2, {}))
     configs.append(("C4b", "disk, 816 rings (~4.0 M triangles), BiCGSTAB mode", lambda: meshes.disk(816), 2, 20, 0, {"solver": 1}))
+    # C4p: the same equation on the mesh SURVEY.md 8(d) specifies -- Triangle's unstructured output, boundary flags from its point markers
+    configs.append(("C4p", "PSLG disk: 4096-gon R=57.3 through the reference's Triangle hand-off, area 0.004", pslg_disk, 2, 20, 2, {}))
     only = set(x for x in args.only.split(",") if x)
     for name, desc, mesh_fn, eq, gpu_steps, cpu_steps, solver in configs:
         if only and name not in only:
             continue
-        xyz, tri = mesh_fn()
-        xyz = np.ascontiguousarray(xyz, np.float32)
-        tri = np.ascontiguousarray(tri, np.uint32)
+        mesh = mesh_fn()
+        if mesh is None:
+            print(json.dumps({"config": name, "skipped": "oracle/_ref/libfea_surface_ref.so not present (mesh generator)"}), flush=True)
+            continue
+        xyz = np.ascontiguousarray(mesh[0], np.float32)
+        tri = np.ascontiguousarray(mesh[1], np.uint32)
         V = len(xyz)
-        ob = meshes.boundary_flags(V, tri)
+        ob = np.ascontiguousarray(mesh[2], np.uint8) if len(mesh) > 2 else meshes.boundary_flags(V, tri)
         seeds = meshes.seed_nodes(V)
         F = feab.Feab(real=64)
         if solver:
