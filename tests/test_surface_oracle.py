@@ -159,3 +159,20 @@ def test_obj_reader_matches_reference_ingest(tmp_path):
     n.write_text("v 0 0 0\nv 1 0 0\nv 0 1 0\nf 1 2 3\n")
     with pytest.raises(feab.FeabError, match="does not contain normals"):
         surface.parse_obj(str(n))
+
+
+@needs_ref
+def test_pslg_disk_generator_of_config_c4():
+    """bench_configs.pslg_disk: the reference's Triangle hand-off ("Qeqpza0.004") on a regular polygon.  Triangle count follows
+    SURVEY.md 8(d)'s T ~ pi R^2 / (0.6 area); the boundary flags Triangle's point markers give are the edge-count flags."""
+    import bench_configs as B
+    xyz, tri, ob = B.pslg_disk(radius=10.0, sides=512)
+    T = len(tri)
+    assert abs(T / (np.pi * 100.0 / (0.6 * 0.004)) - 1.0) < 0.10
+    assert (xyz[:, 1] == 0).all() and tri.max() < len(xyz)
+    assert ((ob != 0) == (meshes.boundary_flags(len(xyz), tri) != 0)).all() and int((ob != 0).sum()) == 512
+    # winding: Surface::perform_triangulation reverses Triangle's counter-clockwise order (src/Utils/Surface.cpp:467-469),
+    # which makes the normals of the XZ-plane disk point along +y
+    a, b, c = xyz[tri[:, 0]], xyz[tri[:, 1]], xyz[tri[:, 2]]
+    ny = np.cross(b - a, c - a)[:, 1]
+    assert (ny > 0).all() or (ny < 0).all()
