@@ -140,7 +140,7 @@ def seed_protocol(F, V, nsteps):
 
 
 # ------------------------------------------------------------------------------------------------ CPU reference
-def cpu_reference(sample_nu, steps, warmup, threads, target_rows=None):
+def cpu_reference(sample_nu, steps, warmup, threads, target_rows=None, single_thread_steps=0):
     """Times the UNMODIFIED reference (Eigen fp32 Jacobi-PCG, oracle/_ref/libfea_ref_fast.so) on a bounded sample of
     the workload: the same Gray-Scott protocol on a smaller icosphere from the same generator with the same element
     size (so the PCG iteration counts are those of the full mesh).  Returns steps/s of the sample and the figure
@@ -173,7 +173,17 @@ def cpu_reference(sample_nu, steps, warmup, threads, target_rows=None):
             times.append(dt)
         done += 1
     sps = len(times) / sum(times)
-    out = {"sample_steps_per_s": sps, "sample_rows": V, "assembly_s": t_asm, "cores": used, "kind": "reference",
+    single = None
+    if single_thread_steps > 0 and fast and used > 1:
+        # what the reference ships (no OpenMP in its CMakeLists.txt:106): the same steady-state steps on one thread
+        R.set_threads(1)
+        t1 = []
+        for _ in range(single_thread_steps):
+            t0 = time.perf_counter()
+            R.step(1)
+            t1.append(time.perf_counter() - t0)
+        single = len(t1) / sum(t1)
+    out = {"sample_steps_per_s": sps, "sample_steps_per_s_1_thread": single, "sample_rows": V, "assembly_s": t_asm, "cores": used, "kind": "reference",
            "build": "fast(-O3 -march=x86-64-v3 -fopenmp)" if fast else "pin(-O2)"}
     if target_rows:
         ratio = target_rows / V              # same element size and dt => same PCG iteration counts; work ~ rows
@@ -396,11 +406,14 @@ def main():
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
-        res = cpu_reference(args.cpu_nu, args.cpu_steps, 1, ncores, target_rows=V)
+        res = cpu_reference(args.cpu_nu, args.cpu_steps, 1, ncores, target_rows=V, single_thread_steps=2)
         if res is not None:
             cpu = {"value": res["converted_steps_per_s"], "unit": "steps/s", "cores": res["cores"], "kind": res["kind"],
                    "sample": f"{res['sample_steps_per_s']:.4f} steps/s measured on icosphere nu={args.cpu_nu} ({res['sample_rows']} rows, "
                              f"{args.cpu_steps} steps, fp32 Eigen PCG tol 1.19e-7), converted by {res['conversion']}; {res['build']}"}
+            if res.get("sample_steps_per_s_1_thread"):
+                # the reference as shipped is single-threaded; same sample, same conversion
+                cpu["single_thread_value"] = res["sample_steps_per_s_1_thread"] * res["converted_steps_per_s"] / res["sample_steps_per_s"]
 
     if rank == 0:
         total_steps = args.steps              # one mesh: N ranks advance the same time step together
