@@ -9,17 +9,38 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libfeab.so")
 SOURCES = ["feab.cu", "surface.cu", "ply_writer.cpp"]
-HEADERS = ["common.cuh", "pattern.cuh", "assembly.cuh", "solver.cuh", "bicgstab.cuh", "spmv_tma.cuh", "comm.cuh", "partition.cuh", "pcg_persistent.cuh", "rhs_tma.cuh", "surface_kernels.cuh", "ply_kernels.cuh", "pick_kernels.cuh", "ply_writer.hpp",
-           os.path.join("..", "..", "include", "feab_surface.h"),
-           os.path.join("..", "..", "include", "feab.h")]
+
+
+def _deps():
+    """Everything libfeab.so is built from: every file under csrc/ and the C-ABI headers (globbed, so that a new
+    header can never be forgotten here)."""
+    inc = os.path.join(HERE, "..", "include")
+    out = [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC)) if f.endswith((".cu", ".cuh", ".cpp", ".hpp", ".h"))]
+    out += [os.path.join(inc, f) for f in sorted(os.listdir(inc)) if f.endswith(".h")]
+    return out
+
+
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC,-ffp-contract=off", "-shared"]
 
 
+HASHFILE = LIB + ".srchash"
+
+
+def source_hash() -> str:
+    """sha256 over the contents of every build input + the flags: libfeab.so is rebuilt whenever this differs from the
+    hash recorded next to it (mtimes do not survive a checkout or the copy to the GPU box)."""
+    import hashlib
+    h = hashlib.sha256(" ".join(NVCC_FLAGS).encode())
+    for f in _deps():
+        h.update(os.path.basename(f).encode())
+        h.update(open(f, "rb").read())
+    return h.hexdigest()
+
+
 def stale() -> bool:
-    if not os.path.exists(LIB):
+    if not os.path.exists(LIB) or not os.path.exists(HASHFILE):
         return True
-    t = os.path.getmtime(LIB)
-    return any(os.path.getmtime(os.path.join(CSRC, f)) > t for f in SOURCES + HEADERS)
+    return open(HASHFILE).read().strip() != source_hash()
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
@@ -35,6 +56,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
         sys.stderr.write(out.stdout + out.stderr)
     if out.returncode != 0:
         raise RuntimeError("nvcc failed building libfeab.so")
+    with open(HASHFILE, "w") as f:
+        f.write(source_hash() + "\n")
     return LIB
 
 

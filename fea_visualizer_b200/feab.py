@@ -66,6 +66,19 @@ def load_library() -> C.CDLL:
     """Loads the in-tree libfeab.so.  Raises if it has not been built (python -m fea_visualizer_b200.build)."""
     global _lib
     if _lib is None:
+        # never run a binary older than its sources: rebuild (nvcc, under a file lock so that torchrun ranks do not race)
+        # when the recorded source hash differs.  FEAB_NO_REBUILD=1 skips the check.
+        if os.environ.get("FEAB_NO_REBUILD") != "1":
+            try:
+                import fcntl
+                from . import build as _build
+                with open(os.path.join(HERE, ".build.lock"), "w") as lk:
+                    fcntl.flock(lk, fcntl.LOCK_EX)
+                    if _build.stale():
+                        _build.build()
+            except Exception as e:  # no nvcc here: fall through to whatever is built, loudly
+                import sys
+                sys.stderr.write(f"[feab] libfeab.so could not be checked / rebuilt against its sources: {e}\n")
         if not os.path.exists(LIB_PATH):
             raise FileNotFoundError(f"{LIB_PATH} not built; run __graft_entry__.build() (nvcc, sm_100a). There is no CPU fallback.")
         lib = C.CDLL(LIB_PATH)

@@ -67,6 +67,8 @@ def assets():
     out = {}
     ref = "/root/reference/assets/fem_meshes"
     for name, steps in (("icosphere", 100), ("tube", 20)):
+        # tube.obj is all quads; meshes.load_obj splits them as a fan (0,1,2),(0,2,3).  tinyobjloader (empty submodule in
+        # the snapshot) is NOT available, so the tube/* arrays pin the reference's FEM code on this repo's split rule only.
         xyz, tri = meshes.load_obj(os.path.join(ref, name + ".obj"))
         ob = meshes.boundary_flags(len(xyz), tri)
         out[f"{name}/xyz"] = xyz

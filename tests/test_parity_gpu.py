@@ -176,6 +176,9 @@ def test_c1_heat_100_steps_on_bundled_icosphere():
 
 
 def test_tube_all_equations_vs_reference_golden():
+    # CAVEAT: tube.obj is all quads and lib/tinyobjloader is an empty submodule in the snapshot, so the
+    # quad -> triangle split in these fixtures is THIS repo's fan rule (meshes.load_obj), not tinyobjloader's: the fields
+    # below pin FEMContext.cpp + CPUSolver.cpp on that triangulation, they do not pin the reference's OBJ polygon split.
     g = load_golden("ref_assets.npz")
     xyz, tri, ob = g["tube/xyz"], g["tube/tri"].astype(np.uint32), g["tube/onb"]
     for bc in (0, 1):

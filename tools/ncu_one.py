@@ -1,5 +1,5 @@
 """Tiny driver for ncu captures: build the 16M Gray-Scott operator and launch one hot kernel a few times.
-usage: python scratch/ncu_one.py <nu> <kernel id 0..3> <reps> [real]"""
+usage: python tools/ncu_one.py <nu> <kernel id 0..3> <reps> [real]"""
 import sys, numpy as np
 sys.path.insert(0, '.')
 from fea_visualizer_b200 import feab, meshes
