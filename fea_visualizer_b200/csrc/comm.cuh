@@ -12,7 +12,9 @@
 //     boundary tile, so the interior rows overlap the transfer.
 // Double buffering by sequence parity is sufficient: a rank can publish all-reduce s+2 only after it consumed
 // s+1, which needs every peer's s+1, which each peer publishes after consuming s.
-// All spins are bounded (kSpinTimeoutNs): on timeout the kernel records an error and carries on, the host reports it.
+// All spins are bounded (kSpinTimeoutNs) and FAIL CLOSED: on timeout the waiting kernel records CommLocal::error, stops
+// the solve (every CTA of a persistent kernel takes the same exit at the same grid sync), later kernels of the step
+// return at once without touching values / u / v or pushing anything to a peer, and the host raises FEAB_ECOMM.
 #pragma once
 #include "common.cuh"
 
@@ -41,7 +43,23 @@ struct CommLocal {  // private to the rank
     unsigned long long root_seq;
     unsigned int ticket;
     int error;
+    // grid-wide syncs of the persistent kernels (gsync_* below): arrivals at the current sync (atomicInc wraps it back to 0
+    // with the last arrival, so it never needs a reset) and the number of barrier-only syncs released so far
+    unsigned int gs_arrive;
+    int err_kind;                  // which wait gave up first: 1 halo flag, 2 state flag, 3 full-values flag, 4 root flag,
+                                   // 5 mailbox word of an all-reduce, 6 grid sync of the own rank
+    unsigned long long gs_release;
+    unsigned long long err_want;   // the flag value / sequence number that never arrived
+    int err_peer;                  // the rank it was expected from
+    int err_pad;
 };
+__device__ __forceinline__ void comm_fail(CommLocal* loc, int kind, unsigned long long want, int peer) {
+    if (atomicCAS(&loc->error, 0, 1) == 0) {
+        loc->err_kind = kind;
+        loc->err_want = want;
+        loc->err_peer = peer;
+    }
+}
 constexpr size_t kCtrlBytes = (sizeof(CommCtrl) + 255) / 256 * 256;
 
 // Passed by value to kernels.  world == 1: nothing below is touched.
@@ -104,18 +122,20 @@ __global__ void build_push_table(HaloPlan hp, int* __restrict__ tab) {
 }
 
 // Spin until *flag >= want (one thread).  Returns false on timeout.
-__device__ __forceinline__ bool spin_until_ge(const unsigned long long* flag, unsigned long long want, CommLocal* loc) {
+__device__ __forceinline__ bool spin_until_ge(const unsigned long long* flag, unsigned long long want, CommLocal* loc, int kind = 0,
+                                              int peer = -1) {
     if (ld_acquire_sys(flag) >= want) return true;
     const unsigned long long t0 = globaltimer_ns();
     while (ld_acquire_sys(flag) < want) {
         __nanosleep(64);
-        if (globaltimer_ns() - t0 > kSpinTimeoutNs) {
-            loc->error = 1;
+        if (globaltimer_ns() - t0 > kSpinTimeoutNs || *(volatile int*)&loc->error) {  // a wait that already failed fails the rest at once
+            comm_fail(loc, kind, want, peer);
             return false;
         }
     }
     return true;
 }
+__device__ __forceinline__ bool comm_failed(const Comm& cm) { return *(volatile int*)&cm.loc->error != 0; }
 
 // LL mailbox: store value k of all-reduce `seq` into a (possibly remote) slot / wait for it in a local slot.
 __device__ __forceinline__ void ll_store(ArSlot* sl, int k, double v, unsigned long long seq) {
@@ -124,7 +144,8 @@ __device__ __forceinline__ void ll_store(ArSlot* sl, int k, double v, unsigned l
     st_volatile_u64(&sl->w[2 * k], flag | (bits & 0xffffffffull));
     st_volatile_u64(&sl->w[2 * k + 1], flag | (bits >> 32));
 }
-__device__ __forceinline__ double ll_wait(const ArSlot* sl, int k, unsigned long long seq, CommLocal* loc) {
+// *ok is cleared (and CommLocal::error set) when the word never arrived; the caller must not use the value then.
+__device__ __forceinline__ double ll_wait(const ArSlot* sl, int k, unsigned long long seq, CommLocal* loc, bool* ok = nullptr, int peer = -1) {
     const unsigned long long flag = seq & 0xffffffffull;
     unsigned long long lo = ld_volatile_u64(&sl->w[2 * k]), hi = ld_volatile_u64(&sl->w[2 * k + 1]);
     if ((lo >> 32) != flag || (hi >> 32) != flag) {
@@ -133,8 +154,9 @@ __device__ __forceinline__ double ll_wait(const ArSlot* sl, int k, unsigned long
             lo = ld_volatile_u64(&sl->w[2 * k]);
             hi = ld_volatile_u64(&sl->w[2 * k + 1]);
             if ((lo >> 32) == flag && (hi >> 32) == flag) break;
-            if (globaltimer_ns() - t0 > kSpinTimeoutNs) {
-                loc->error = 1;
+            if (globaltimer_ns() - t0 > kSpinTimeoutNs || *(volatile int*)&loc->error) {
+                comm_fail(loc, 5, seq, peer);
+                if (ok) *ok = false;
                 break;
             }
         }
@@ -154,9 +176,11 @@ __device__ __forceinline__ T sum_partials_cg(const T* part, int count, T* sm) {
 }
 
 // Producer side.  Call from ALL threads of EVERY CTA after thread 0 stored part[k * stride + blockIdx.x], k < K.
-// The last CTA to arrive publishes the rank totals to every rank.
+// The last CTA to arrive publishes the rank totals to every rank (its own mailbox included, so the consumer is the same
+// code on 1..8 ranks).  raise_halo: the kernel also stored boundary rows into the neighbours' ghost tails (every CTA that
+// did ran a system-scope fence before calling this); the last CTA then raises the neighbours' halo flags.
 template <typename R, int K, int NW = kBlock / 32>
-__device__ __forceinline__ void ar_publish(const Comm& cm, const R* part, int stride, R* sm) {
+__device__ __forceinline__ void ar_publish(const Comm& cm, const R* part, int stride, R* sm, const HaloPlan* hp = nullptr, bool raise_halo = false) {
     __shared__ int s_last;
     if (threadIdx.x == 0) {
         __threadfence();
@@ -178,6 +202,21 @@ __device__ __forceinline__ void ar_publish(const Comm& cm, const R* part, int st
 #pragma unroll
             for (int k = 0; k < K; k++) ll_store(sl, k, (double)tot[k], s);
         }
+        if (raise_halo && hp != nullptr) {
+            const unsigned long long hs = cm.loc->halo_seq + 1;
+            cm.loc->halo_seq = hs;
+            for (int b = 0; b < hp->nnb; b++) st_release_sys(&cm.ctrl[hp->nb_rank[b]]->halo_flag[cm.rank], hs);
+        }
+    }
+}
+
+// Boundary row `row` (>= hp.n_int) of arena vector `vec`: mirror `val` on every neighbour that keeps the row as a ghost.
+template <typename R>
+__device__ __forceinline__ void push_boundary_row(const HaloPlan& hp, int vec, int64_t row, R val) {
+    const int* t = hp.push_tab + (size_t)(row - hp.n_int) * hp.nnb;
+    for (int b = 0; b < hp.nnb; b++) {
+        const int d = t[b];
+        if (d >= 0) reinterpret_cast<R*>(hp.base[hp.nb_rank[b]] + hp.off_vec[vec][hp.nb_rank[b]])[d] = val;
     }
 }
 
@@ -215,18 +254,128 @@ __global__ void ar_collect(Comm cm, R* __restrict__ totals) {
         for (int k = 0; k < K; k++) totals[k] = t[k];
 }
 
+// K sums of gridDim.x per-CTA partials written before a grid sync (partials of sum k at part + k * stride), added in
+// CTA order: one pass over L2, one block reduction.  Result in every thread of the calling CTA.
+template <typename R, int K, int NW>
+__device__ __forceinline__ void sum_cta_partials_vec(const R* part, size_t stride, R (&out)[K], R* red /* (NW + 1) * K */) {
+#pragma unroll
+    for (int k = 0; k < K; k++) out[k] = (R)0;
+    for (int i = threadIdx.x; i < (int)gridDim.x; i += blockDim.x) {
+#pragma unroll
+        for (int k = 0; k < K; k++) out[k] += __ldcg(part + k * stride + i);
+    }
+    block_sum_vec<R, K, NW>(out, red);
+}
+
+// ---- grid-wide syncs of the persistent (cooperative) kernels, merged with the all-reduce that rides on them ----------
+// gsync_allreduce: every CTA of every rank calls it with its K partial sums.  Thread 0 stores the CTA's partials, fences
+// and takes a ticket; the LAST CTA of the rank to arrive adds all partials in CTA order and stores the rank totals, as LL
+// words, into EVERY rank's mailbox (its own included: one code path for 1..8 ranks); every CTA then waits -- directly on
+// the mailbox words, there is no separate arrival counter to spin on -- for the totals of all ranks and adds them in rank
+// order.  Bit-identical results in every CTA of every rank, so all of them take the same decisions.  One wait where the
+// first version had three (barrier -> every CTA re-sums all partials -> mailbox exchange).  The sync also orders memory:
+// what any CTA of the rank wrote before it is visible to every CTA after it (fence / ticket / LL word / fence).
+// Returns false when a peer never answered (CTA-uniform, and the same in every CTA of the rank: all of them sit in the
+// same sync when a peer dies).  s_ctl[1] must be zero when the kernel starts.
+template <typename R, int K, int NW>
+__device__ __forceinline__ bool gsync_allreduce(const Comm& cm, unsigned long long& seq, R* __restrict__ part /* K x gridDim.x */,
+                                                R (&v)[K] /* in: this CTA's partials (thread 0); out: the global sums */,
+                                                R* red /* (NW + 1) * K */, double* s_pk /* kMaxRanks * 4 */, int* s_ctl /* 2 */) {
+    static_assert(K >= 1 && K <= 4, "an ArSlot carries four values");
+    const unsigned G = gridDim.x;
+    seq += 1;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int k = 0; k < K; k++) part[(size_t)k * G + blockIdx.x] = v[k];
+        __threadfence();
+        s_ctl[0] = atomicInc(&cm.loc->gs_arrive, G - 1u) == G - 1u ? 1 : 0;  // wraps to 0 with the last arrival
+    }
+    __syncthreads();
+    if (s_ctl[0]) {  // the last CTA of this rank: every other CTA's partials (and phase stores) are visible after the fence
+        __threadfence();
+        R tot[K];
+        sum_cta_partials_vec<R, K, NW>(part, (size_t)G, tot, red);
+        if ((int)threadIdx.x < cm.world) {
+            ArSlot* sl = &cm.ctrl[threadIdx.x]->slot[seq & 1][cm.rank];
+#pragma unroll
+            for (int k = 0; k < K; k++) ll_store(sl, k, (double)tot[k], seq);
+        }
+        if (threadIdx.x == 0) cm.loc->ar_seq = seq;
+    }
+    if ((int)threadIdx.x < cm.world) {
+        const ArSlot* mine = &cm.ctrl[cm.rank]->slot[seq & 1][threadIdx.x];
+        bool ok = true;
+#pragma unroll
+        for (int k = 0; k < K; k++) s_pk[threadIdx.x * 4 + k] = ll_wait(mine, k, seq, cm.loc, &ok, (int)threadIdx.x);
+        if (!ok) s_ctl[1] = 1;
+        __threadfence();
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < K; k++) {
+        R acc = (R)0;
+        for (int w = 0; w < cm.world; w++) acc += (R)s_pk[w * 4 + k];
+        v[k] = acc;
+    }
+    const bool failed = s_ctl[1] != 0;
+    __syncthreads();
+    return !failed;
+}
+
+// Barrier-only sync of the rank's grid (no value travels).  halo_seq != 0: the phase before it pushed boundary rows into
+// the neighbours' ghost tails (each pushing CTA ran a system-scope fence before arriving); the last CTA to arrive raises
+// the neighbours' halo flags with release stores, one thread per neighbour, AFTER letting its own rank go on.
+__device__ __forceinline__ bool gsync_barrier(const Comm& cm, const HaloPlan& hp, unsigned long long& bseq, unsigned long long halo_seq,
+                                              int* s_ctl /* 2 */) {
+    const unsigned G = gridDim.x;
+    bseq += 1;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        s_ctl[0] = atomicInc(&cm.loc->gs_arrive, G - 1u) == G - 1u ? 1 : 0;
+    }
+    __syncthreads();
+    if (s_ctl[0]) {
+        if (threadIdx.x == 0) {
+            __threadfence();
+            st_volatile_u64(&cm.loc->gs_release, bseq);
+            if (halo_seq) cm.loc->halo_seq = halo_seq;
+        }
+        if (halo_seq && (int)threadIdx.x < hp.nnb) st_release_sys(&cm.ctrl[hp.nb_rank[threadIdx.x]]->halo_flag[cm.rank], halo_seq);
+    } else if (threadIdx.x == 0) {
+        if (ld_volatile_u64(&cm.loc->gs_release) < bseq) {
+            const unsigned long long t0 = globaltimer_ns();
+            while (ld_volatile_u64(&cm.loc->gs_release) < bseq) {
+                if (globaltimer_ns() - t0 > kSpinTimeoutNs || *(volatile int*)&cm.loc->error) {
+                    comm_fail(cm.loc, 6, bseq, cm.rank);
+                    s_ctl[1] = 1;
+                    break;
+                }
+            }
+        }
+        __threadfence();
+    }
+    __syncthreads();
+    const bool failed = s_ctl[1] != 0;
+    __syncthreads();
+    return !failed;
+}
+
 // Wait (one thread) until every neighbour's push number `want` has landed.  kind: 0 halo, 1 state, 2 full.
-__device__ __forceinline__ void wait_flags(const Comm& cm, const HaloPlan& hp, int kind, unsigned long long want) {
+__device__ __forceinline__ bool wait_flags(const Comm& cm, const HaloPlan& hp, int kind, unsigned long long want) {
     const CommCtrl* me = cm.ctrl[cm.rank];
+    bool ok = true;
     if (kind == 2) {
         for (int q = 0; q < cm.world; q++)
-            if (q != cm.rank) spin_until_ge(&me->full_flag[q], want, cm.loc);
-        return;
+            if (q != cm.rank) ok = spin_until_ge(&me->full_flag[q], want, cm.loc, 3, q) && ok;
+        return ok;
     }
     for (int i = 0; i < hp.nnb; i++) {
         const int q = hp.nb_rank[i];
-        spin_until_ge(kind == 0 ? &me->halo_flag[q] : &me->state_flag[q], want, cm.loc);
+        ok = spin_until_ge(kind == 0 ? &me->halo_flag[q] : &me->state_flag[q], want, cm.loc, kind == 0 ? 1 : 2, q) && ok;
     }
+    return ok;
 }
 __global__ void wait_kernel(Comm cm, HaloPlan hp, int kind) {
     if (threadIdx.x == 0) {
@@ -350,7 +499,7 @@ __global__ void root_wait(Comm cm) {
     if (threadIdx.x == 0) {
         const unsigned long long s = cm.loc->root_seq + 1;
         cm.loc->root_seq = s;
-        spin_until_ge(&cm.ctrl[cm.rank]->root_flag, s, cm.loc);
+        spin_until_ge(&cm.ctrl[cm.rank]->root_flag, s, cm.loc, 4, 0);
     }
 }
 

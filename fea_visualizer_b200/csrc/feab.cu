@@ -182,8 +182,6 @@ class SolverT final : public SolverBase {
         CK(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device_));
         pcg_max_grid_ = coop ? occ * sms_ : 0;
         if (const char* v = getenv("FEAB_PCG_CTAS_PER_SM")) pcg_max_grid_ = std::min(pcg_max_grid_, std::max(1, atoi(v)) * sms_);
-        CK(cudaMalloc(&d_bar_, 4 * sizeof(unsigned long long)));
-        CK(cudaMemset(d_bar_, 0, 4 * sizeof(unsigned long long)));
         for (int i = 0; i < 4; i++) CK(cudaEventCreate(&ev_solve_[i]));
         if (const char* v = getenv("FEAB_PCG_PROF")) {  // 1: stamps of pcg_persistent, 2: stamps of pcg_dual
             prof_dual_ = atoi(v) == 2;
@@ -202,6 +200,13 @@ class SolverT final : public SolverBase {
         dual_max_grid_ = coop ? docc * sms_ : 0;
         if (dual_max_grid_ > 0) d_dpart_.alloc((size_t)6 * dual_max_grid_);
         if (const char* v = getenv("FEAB_DUAL")) dual_ = atoi(v) != 0;
+        // several handles whose persistent kernels must be co-resident on ONE device (the threaded virtual-rank tests)
+        if (const char* v = getenv("FEAB_PCG_MAX_GRID")) {
+            const int g = std::max(1, atoi(v));
+            pcg_max_grid_ = std::min(pcg_max_grid_, g);
+            dual_max_grid_ = std::min(dual_max_grid_, g);
+            grid_cap_ = g;  // also for the RHS kernel, whose CTAs wait for the neighbours' state flags
+        }
     }
     static constexpr int kPcgRows = 512, kPcgCpr = 8, kPcgStages = 2, kPcgMinB = 2;
     static constexpr int kDualRows = 256;
@@ -264,7 +269,6 @@ class SolverT final : public SolverBase {
         if (d_st_) cudaFree(d_st_);
         if (d_bst_) cudaFree(d_bst_);
         if (d_loc_) cudaFree(d_loc_);
-        if (d_bar_) cudaFree(d_bar_);
         if (d_prof_) cudaFree(d_prof_);
         for (int i = 0; i < 4; i++)
             if (ev_solve_[i]) cudaEventDestroy(ev_solve_[i]);
@@ -582,6 +586,7 @@ class SolverT final : public SolverBase {
         CK(cudaMemsetAsync(d_u_.p, 0, nc * sizeof(R), stream_));
         CK(cudaMemsetAsync(d_v_.p, 0, nc * sizeof(R), stream_));
         CK(cudaStreamSynchronize(stream_));
+        values_dirty_ = true;
     }
 
     void assemble(const float* vel) override {
@@ -663,6 +668,7 @@ class SolverT final : public SolverBase {
     // ---------------------------------------------------------------- parameters / state
     void set_equation(int eq) override {
         REQUIRE(eq >= 0 && eq <= 3, FEAB_EINVAL, "set_equation: equation must be 0..3");
+        if (eq != eq_) values_dirty_ = true;  // another vector takes surface->values now
         eq_ = eq;
     }
     void set_params(int eq, const FeabParams* p) override {
@@ -694,12 +700,14 @@ class SolverT final : public SolverBase {
         CK(cudaMemsetAsync(d_values_.p, 0, V_ * sizeof(float), stream_));
         CK(cudaMemsetAsync(d_unstable_, 0, sizeof(int), stream_));
         CK(cudaStreamSynchronize(stream_));
+        values_dirty_ = true;
     }
     void set_values(const float* v) override {
         REQUIRE(have_mesh_ && v, FEAB_ENOMESH, "set_values: no mesh");
         CK(cudaSetDevice(device_));
         CK(cudaMemcpyAsync(d_values_.p, v, V_ * sizeof(float), cudaMemcpyHostToDevice, stream_));
         CK(cudaStreamSynchronize(stream_));
+        values_dirty_ = true;
     }
     const float* values_device() override {
         REQUIRE(have_mesh_, FEAB_ENOMESH, "values_device: no mesh");
@@ -723,6 +731,7 @@ class SolverT final : public SolverBase {
         launches_++;
         CK(cudaGetLastError());
         CK(cudaStreamSynchronize(stream_));
+        values_dirty_ = true;
     }
     void get_state(int which, void* out) override {
         REQUIRE(have_mesh_ && out && (which == 0 || which == 1), FEAB_EINVAL, "get_state: bad arguments");
@@ -733,13 +742,14 @@ class SolverT final : public SolverBase {
         REQUIRE(have_mesh_ && in && (which == 0 || which == 1), FEAB_EINVAL, "set_state: bad arguments");
         CK(cudaSetDevice(device_));
         CK(cudaMemcpy(which == 0 ? d_u_.p : d_v_.p, in, n_ * sizeof(R), cudaMemcpyHostToDevice));
+        values_dirty_ = true;  // as before: the next step re-reads the vector surface->values feeds from values
     }
     int unstable() override {
         REQUIRE(have_mesh_, FEAB_ENOMESH, "unstable: no mesh");
         CK(cudaSetDevice(device_));
         int f = 0;
         CK(cudaMemcpy(&f, d_unstable_, sizeof(int), cudaMemcpyDeviceToHost));
-        return f;
+        return f != 0 && f == last_stamp_;  // finish_step stamps the flag with the step number: set by the LAST step only
     }
 
     // ---------------------------------------------------------------- operator cache (K2)
@@ -749,6 +759,8 @@ class SolverT final : public SolverBase {
         return StepScalars{(double)p.time_step, (double)p.c[0], (double)p.c[1], (double)p.c[2], (double)p.c[3]};
     }
     bool use_bicgstab() const { return eq_ == FEAB_EQ_ADVECTION_DIFFUSION && opt_.solver == FEAB_SOLVER_BICGSTAB; }
+    // BiCGSTAB through the multi-kernel WHILE graph / host-batched loop (bicgstab.cuh) instead of the persistent kernel
+    bool use_bicgstab_legacy() const { return use_bicgstab(); }
 
     void ensure_operator() { ensure_operator_on(stream_); }
     void ensure_operator_on(cudaStream_t s) {
@@ -796,30 +808,33 @@ class SolverT final : public SolverBase {
     // K6: RHS + PCG start.  Heat / advection-diffusion / Gray-Scott stream M/dt through the TMA ring (rhs_tma.cuh); the wave
     // equation (two value arrays) and FEAB_RHS_TMA=0 use the LDG kernel of solver.cuh.  Same bits either way.
     static constexpr int kRhsRows = 512, kRhsCpr = 8, kRhsStages = 2, kRhsMinB = 2;
+    // publish: the kernel's last CTA all-reduces |b|^2, b.D^-1 b into every rank's mailbox (the persistent solve kernels and
+    // every partitioned handle start from there) and, on a partition, the kernel stores the first search directions of the
+    // boundary rows into the neighbours' ghost tails and raises their halo flags.
     template <int EQ>
-    void launch_rhs_tma(cudaStream_t s, const StepScalars& sc, R* prt, const Comm& cm) {
+    void launch_rhs_tma(cudaStream_t s, const StepScalars& sc, R* prt, const Comm& cm, int publish) {
         using Cfg = TmaCfg<R, kRhsRows, kRhsCpr, kRhsStages>;
         const int nt = std::max(1, cdiv64(n_, kRhsRows));
-        const int grid = std::max(1, std::min({nt, kRhsMinB * sms_, g_tile_}));
+        const int grid = std::max(1, std::min({nt, kRhsMinB * sms_, g_tile_, grid_cap_}));
         rhs_init_tma<R, EQ, kRhsRows, kRhsCpr, kRhsStages, kRhsMinB><<<grid, kRhsRows, Cfg::kSmemBytes, s>>>(
             d_rowptr_.p, d_col_.p, d_Md_.p, d_u_.p, d_v_.p, d_dinv0_.p, d_dinv1_.p, n_, nt, sc, d_r_[0].p, d_p_[0].p, d_r_[1].p, d_p_[1].p, prt,
-            g_tile_, cm);
+            g_tile_, cm, hp_, publish);
     }
-    void launch_rhs(cudaStream_t s, const StepScalars& sc, R* prt, const Comm& cm) {
+    void launch_rhs(cudaStream_t s, const StepScalars& sc, R* prt, const Comm& cm, int publish) {
         const size_t sm2 = 2 * kTileCap * sizeof(R);
 #define FEAB_RHS(EQ)                                                                                                             \
     rhs_init<R, EQ><<<g_tile_, kBlock, sm2, s>>>(d_rowptr_.p, d_col_.p, d_Md_.p, d_K_.p, d_u_.p, d_v_.p, d_dinv0_.p, d_dinv1_.p, n_, \
-                                                 num_tiles_, sc, d_r_[0].p, d_p_[0].p, d_r_[1].p, d_p_[1].p, prt, cm)
+                                                 num_tiles_, sc, d_r_[0].p, d_p_[0].p, d_r_[1].p, d_p_[1].p, prt, cm, hp_, publish)
         switch (eq_) {
             case FEAB_EQ_HEAT:
-                if (rhs_tma_) launch_rhs_tma<0>(s, sc, prt, cm); else FEAB_RHS(0);
+                if (rhs_tma_) launch_rhs_tma<0>(s, sc, prt, cm, publish); else FEAB_RHS(0);
                 break;
             case FEAB_EQ_WAVE: FEAB_RHS(1); break;
             case FEAB_EQ_ADVECTION_DIFFUSION:
-                if (rhs_tma_) launch_rhs_tma<2>(s, sc, prt, cm); else FEAB_RHS(2);
+                if (rhs_tma_) launch_rhs_tma<2>(s, sc, prt, cm, publish); else FEAB_RHS(2);
                 break;
             default:
-                if (rhs_tma_) launch_rhs_tma<3>(s, sc, prt, cm); else FEAB_RHS(3);
+                if (rhs_tma_) launch_rhs_tma<3>(s, sc, prt, cm, publish); else FEAB_RHS(3);
                 break;
         }
 #undef FEAB_RHS
@@ -830,28 +845,39 @@ class SolverT final : public SolverBase {
         state_push<R><<<1, 1024, 0, s>>>(cm_, hp_, d_u_.p, d_v_.p, d_values_.p);
         launches_++;
     }
+    // true when the solves of this step start inside a persistent kernel (from the RHS kernel's published sums)
+    bool persistent_solves(bool capturing) const { return !capturing && !lockstep_ && opt_.loop_mode == FEAB_LOOP_PERSISTENT && !use_bicgstab_legacy(); }
     void ph_step_begin(cudaStream_t s, bool capturing) {
         const int gV = cdiv64(V_, kBlock);
         const StepScalars sc = scalars();
-        if (world_ > 1) wait_kernel<<<1, 32, 0, s>>>(cm_, hp_, 1);
-        CK(cudaMemsetAsync(d_unstable_, 0, sizeof(int), s));
-        R* target = eq_ == FEAB_EQ_REACTION_DIFFUSION ? d_v_.p : d_u_.p;
-        gather_values<R><<<gV, kBlock, 0, s>>>(d_values_.p, colmap_p_, V_, target);
-        launch_rhs(s, sc, part_rhs(), cm_);
-        if (!capturing) launches_ += 2;
+        // surface->values -> solver vector only when somebody else wrote values since the last step (brush, set_values, host
+        // upload, ...): the solver's own result is re-read through float by the RHS kernel (solver.cuh through_float).  A
+        // captured graph and the lock-step test driver always gather.
+        const bool gather = values_dirty_ || capturing || lockstep_;
+        if (capturing) CK(cudaMemsetAsync(d_unstable_, 0, sizeof(int), s));
+        if (gather) {
+            R* target = eq_ == FEAB_EQ_REACTION_DIFFUSION ? d_v_.p : d_u_.p;
+            if (world_ > 1) wait_kernel<<<1, 32, 0, s>>>(cm_, hp_, 1);  // ghost values: the neighbours' end-of-step pushes have landed
+            gather_values<R><<<gV, kBlock, 0, s>>>(d_values_.p, colmap_p_, V_, target, cm_, hp_);
+        }
+        const int publish = (world_ > 1 || persistent_solves(capturing)) ? 1 : 0;
+        launch_rhs(s, sc, part_rhs(), cm_, publish);
+        if (!capturing) {
+            launches_ += gather ? (world_ > 1 ? 3 : 2) : 1;
+            values_dirty_ = false;
+        }
         CK(cudaGetLastError());
     }
-    // partitioned: totals of the RHS dot products for cg_begin, first search directions to the neighbours.
+    // partitioned, three-kernel loop drivers only: totals of the RHS dot products for cg_begin.
     // A separate phase: it consumes what EVERY rank's rhs_init published.
     void ph_step_collect(cudaStream_t s, bool capturing) {
-        if (world_ > 1) {
+        if (world_ > 1 && !persistent_solves(capturing)) {
             const bool gs = eq_ == FEAB_EQ_REACTION_DIFFUSION;
             if (gs)
                 ar_collect<R, 4><<<1, 32, 0, s>>>(cm_, d_rhs_tot_.p);
             else
                 ar_collect<R, 2><<<1, 32, 0, s>>>(cm_, d_rhs_tot_.p);
-            halo_push<R><<<1, 1024, 0, s>>>(cm_, hp_, d_p_[0].p, kVecP0, gs ? d_p_[1].p : (const R*)nullptr, kVecP1);
-            if (!capturing) launches_ += 3;
+            if (!capturing) launches_ += 1;
         }
         CK(cudaGetLastError());
     }
@@ -877,12 +903,16 @@ class SolverT final : public SolverBase {
         if (world_ > 1) halo_push<R><<<1, 1024, 0, s>>>(cm_, hp_, d_p_[slot].p, slot == 0 ? kVecP0 : kVecP1, (const R*)nullptr, 0);
     }
     int kernels_per_iteration() const { return world_ > 1 ? 4 : 3; }
+    // epilogue: values <- solution, wave u += v dt, instability stamp; on a partition the owners of boundary rows also store
+    // u, v and the value into the neighbours' ghosts and the last CTA raises the state flags (no separate push kernel)
     void ph_finish(cudaStream_t s, bool capturing) {
         const int gV = cdiv64(V_, kBlock);
+        // a captured graph replays one stamp: it keeps the sticky semantics of a flag that is reset by feab_clear only
+        const int stamp = capturing ? 1 : (step_stamp_ = step_stamp_ >= INT32_MAX - 1 ? 1 : step_stamp_ + 1);
+        if (!capturing) last_stamp_ = stamp;
         finish_step<R><<<gV, kBlock, 0, s>>>(d_values_.p, d_idx_.p, rowmap_p_, V_, d_u_.p, d_v_.p, eq_ == FEAB_EQ_WAVE ? 1 : 0, (R)scalars().dt,
-                                             eq_ == FEAB_EQ_REACTION_DIFFUSION ? 1 : 0, d_unstable_);
-        if (world_ > 1) state_push<R><<<1, 1024, 0, s>>>(cm_, hp_, d_u_.p, d_v_.p, d_values_.p);
-        if (!capturing) launches_ += world_ > 1 ? 2 : 1;
+                                             eq_ == FEAB_EQ_REACTION_DIFFUSION ? 1 : 0, d_unstable_, stamp, cm_, hp_);
+        if (!capturing) launches_ += 1;
         CK(cudaGetLastError());
     }
     // the solves of the current equation: (operator, inverse diagonal, solution vector)
@@ -907,13 +937,10 @@ class SolverT final : public SolverBase {
         return dual_ && !capturing && opt_.loop_mode == FEAB_LOOP_PERSISTENT && eq_ == FEAB_EQ_REACTION_DIFFUSION && dual_max_grid_ > 0 &&
                !use_bicgstab();
     }
-    // Gray-Scott: u- and v-solve advance together until the first of them stops (pcg_dual.cuh), then each is
-    // finished (or found finished) by the single-system kernel, which resumes from CgState.
+    // Gray-Scott: u- and v-solve advance together until the first of them stops (pcg_dual.cuh); the single-system kernel
+    // then finishes whichever is still running (it picks the system from CgState; both done -> it returns at once).
+    // Two launches per step; the start of both solves (thresholds, early-outs) is taken inside pcg_dual.
     void enqueue_dual(const R* const* A, const R* const* dinv, R* const* x) {
-        cudaGraphConditionalHandle none = 0;
-        ph_cg_begin(stream_, 0, x[0], none, 0);
-        ph_cg_begin(stream_, 1, x[1], none, 0);
-        CK(cudaMemsetAsync(d_bar_, 0, 4 * sizeof(unsigned long long), stream_));
         PcgDualArgs<R> da;
         da.rowptr = d_rowptr_.p;
         da.col = d_col_.p;
@@ -930,8 +957,9 @@ class SolverT final : public SolverBase {
         da.num_tiles = std::max(1, cdiv64(n_, kDualRows));
         da.st = d_st_;
         da.part = d_dpart_.p;
-        da.bar = d_bar_;
         da.first_halo_tile = first_halo_tile(kDualRows);
+        da.tol = tol();
+        da.maxit = maxit();
         da.prof = prof_dual_ ? d_prof_ : nullptr;
         const int grid = std::min(dual_max_grid_, da.num_tiles);
         using DCfg = DualCfg<R, kDualRows, kPcgCpr, kPcgStages>;
@@ -939,43 +967,54 @@ class SolverT final : public SolverBase {
         if (time_solves_) CK(cudaEventRecord(ev_solve_[0], stream_));
         CK(cudaLaunchCooperativeKernel((const void*)pcg_dual<R, kDualRows, kPcgCpr, kPcgStages, kPcgMinB>, dim3(grid), dim3(2 * kDualRows), kargs,
                                        DCfg::kSmemBytes, stream_));
-        launches_ += 3;  // 2 x cg_begin + pcg_dual
-        for (int slot = 0; slot < 2; slot++) enqueue_pcg(slot, A[slot], dinv[slot], x[slot], false, true);
+        launches_ += 1;
+        launch_pcg_persistent(-1, 0, A, dinv, x);
         if (time_solves_) CK(cudaEventRecord(ev_solve_[1], stream_));
     }
 
-    void enqueue_pcg(int slot, const R* A, const R* dinv, R* x, bool capturing, bool resume = false) {
+    // slot >= 0: that system; -1: whichever pcg_dual left running.  begin: number of systems whose start this kernel takes
+    // from the RHS kernel's published sums (0: CgState is already set by an earlier kernel of the step).
+    void launch_pcg_persistent(int slot, int begin, const R* const* A, const R* const* dinv, R* const* x) {
+        PcgArgs<R> pa;
+        pa.rowptr = d_rowptr_.p;
+        pa.col = d_col_.p;
+        for (int s = 0; s < 2; s++) {
+            pa.A[s] = A[s];
+            pa.dinv[s] = dinv[s];
+            pa.x[s] = x[s];
+            pa.r[s] = d_r_[s].p;
+            pa.p[s] = d_p_[s].p;
+        }
+        pa.y = d_y_.p;
+        pa.n = n_;
+        pa.num_tiles = std::max(1, cdiv64(n_, kPcgRows));
+        pa.first_halo_tile = first_halo_tile(kPcgRows);
+        pa.st = d_st_;
+        pa.part = d_ppart_.p;
+        pa.slot = slot;
+        pa.begin = begin;
+        pa.tol = tol();
+        pa.maxit = maxit();
+        pa.prof = prof_dual_ ? nullptr : d_prof_;
+        const int grid = std::min(pcg_max_grid_, pa.num_tiles);
+        using PCfg = TmaCfg<R, kPcgRows, kPcgCpr, kPcgStages>;
+        void* kargs[] = {(void*)&pa, (void*)&cm_, (void*)&hp_};
+        CK(cudaLaunchCooperativeKernel((const void*)pcg_persistent<R, kPcgRows, kPcgCpr, kPcgStages, kPcgMinB>, dim3(grid), dim3(kPcgRows), kargs,
+                                       PCfg::kSmemBytes, stream_));
+        launches_ += 1;
+    }
+
+    // num_solves: solves of this step (the first one takes the start of all of them, see launch_pcg_persistent)
+    void enqueue_pcg(int slot, const R* const* Aall, const R* const* dinvall, R* const* xall, bool capturing, int num_solves = 1) {
+        const R* A = Aall[slot];
+        const R* dinv = dinvall[slot];
+        R* x = xall[slot];
         CgState<R>* st = d_st_ + slot;
-        if (!capturing && opt_.loop_mode == FEAB_LOOP_PERSISTENT) {
+        if (!capturing && opt_.loop_mode == FEAB_LOOP_PERSISTENT && !lockstep_) {
             // the whole solve is one cooperative launch: no WHILE node, no host polling (pcg_persistent.cuh)
-            cudaGraphConditionalHandle none = 0;
-            if (!resume) ph_cg_begin(stream_, slot, x, none, 0);
-            CK(cudaMemsetAsync(d_bar_ + 2 * slot, 0, 2 * sizeof(unsigned long long), stream_));
-            PcgArgs<R> pa;
-            pa.rowptr = d_rowptr_.p;
-            pa.col = d_col_.p;
-            pa.A = A;
-            pa.dinv = dinv;
-            pa.x = x;
-            pa.r = d_r_[slot].p;
-            pa.p = d_p_[slot].p;
-            pa.y = d_y_.p;
-            pa.n = n_;
-            pa.num_tiles = std::max(1, cdiv64(n_, kPcgRows));
-            pa.first_halo_tile = first_halo_tile(kPcgRows);
-            pa.st = st;
-            pa.part = d_ppart_.p;
-            pa.bar = d_bar_ + 2 * slot;
-            pa.vec_p = slot == 0 ? kVecP0 : kVecP1;
-            pa.prof = prof_dual_ ? nullptr : d_prof_;
-            const int grid = std::min(pcg_max_grid_, pa.num_tiles);
-            using PCfg = TmaCfg<R, kPcgRows, kPcgCpr, kPcgStages>;
-            void* kargs[] = {(void*)&pa, (void*)&cm_, (void*)&hp_};
-            if (time_solves_ && !resume) CK(cudaEventRecord(ev_solve_[2 * slot], stream_));
-            CK(cudaLaunchCooperativeKernel((const void*)pcg_persistent<R, kPcgRows, kPcgCpr, kPcgStages, kPcgMinB>, dim3(grid), dim3(kPcgRows), kargs,
-                                           PCfg::kSmemBytes, stream_));
-            if (time_solves_ && !resume) CK(cudaEventRecord(ev_solve_[2 * slot + 1], stream_));
-            launches_ += resume ? 1 : 2;
+            if (time_solves_) CK(cudaEventRecord(ev_solve_[2 * slot], stream_));
+            launch_pcg_persistent(slot, slot == 0 ? num_solves : 0, Aall, dinvall, xall);
+            if (time_solves_) CK(cudaEventRecord(ev_solve_[2 * slot + 1], stream_));
             return;
         }
         if (capturing) {
@@ -1034,7 +1073,7 @@ class SolverT final : public SolverBase {
             if (dual_last_)
                 enqueue_dual(A, dinv, x);
             else
-                for (int slot = 0; slot < ns; slot++) enqueue_pcg(slot, A[slot], dinv[slot], x[slot], capturing);
+                for (int slot = 0; slot < ns; slot++) enqueue_pcg(slot, A, dinv, x, capturing, ns);
         }
         ph_finish(stream_, capturing);
     }
@@ -1076,8 +1115,18 @@ class SolverT final : public SolverBase {
         CommLocal l;
         CK(cudaMemcpy(&l, d_loc_, sizeof(l), cudaMemcpyDeviceToHost));
         if (l.error) {
-            CK(cudaMemset(&d_loc_->error, 0, sizeof(int)));
-            throw Err{FEAB_ECOMM, "step: timed out waiting for a peer (halo flag or all-reduce slot never arrived)"};
+            // the grid-sync / ticket counters of the kernels that gave up are meaningless now
+            l.error = 0;
+            l.ticket = 0;
+            l.gs_arrive = 0;
+            const int kind = l.err_kind, peer = l.err_peer;
+            const unsigned long long want = l.err_want;
+            l.err_kind = 0;
+            CK(cudaMemcpy(d_loc_, &l, sizeof(l), cudaMemcpyHostToDevice));
+            static const char* names[] = {"?", "halo flag", "state flag", "full-values flag", "root flag", "all-reduce mailbox word", "grid sync of this rank"};
+            throw Err{FEAB_ECOMM, std::string("step: rank ") + std::to_string(rank_) + " timed out waiting for " + names[kind >= 0 && kind <= 6 ? kind : 0] +
+                                      " #" + std::to_string(want) + " of rank " + std::to_string(peer) +
+                                      "; the solve was abandoned, values were not written back (feab_clear / reconnect before stepping again)"};
         }
     }
     // surface->values complete on every rank: owners broadcast, everybody waits for everybody
@@ -1099,6 +1148,7 @@ class SolverT final : public SolverBase {
         // Safe against the previous call: rank 0 gets here only after its wait for every peer's values_broadcast of
         // that call, i.e. after the peers' last read of their mirrors.
         const bool root_mode = world_ > 1 && sync == FEAB_SYNC_ROOT && values != nullptr;
+        if (values) values_dirty_ = true;
         if (root_mode) {
             if (rank_ == 0) {
                 CK(cudaMemcpyAsync(d_values_.p, values, V_ * sizeof(float), cudaMemcpyHostToDevice, stream_));
@@ -1116,7 +1166,10 @@ class SolverT final : public SolverBase {
             // BiCGSTAB has no persistent kernel: it keeps the WHILE graph unless host batching was asked for
             const bool graph_mode = opt_.loop_mode == FEAB_LOOP_GRAPH_WHILE || (opt_.loop_mode == FEAB_LOOP_PERSISTENT && use_bicgstab());
             graph_mode_last_ = graph_mode;
-            if (graph_mode) dual_last_ = false;  // a graph replays separate solves
+            if (graph_mode) {
+                dual_last_ = false;  // a graph replays separate solves
+                last_stamp_ = 1;     // ... and one instability stamp (the graph resets the flag at its head)
+            }
             if (graph_mode && (!graph_exec_ || graph_eq_ != eq_)) build_graph();
             for (int s = 0; s < nsteps; s++) {
                 time_solves_ = !graph_mode && opt_.loop_mode == FEAB_LOOP_PERSISTENT && s == nsteps - 1;
@@ -1162,7 +1215,7 @@ class SolverT final : public SolverBase {
         CgState<R> st[2];
         BicgState<R> b;
         read_states(st, &b);
-        int64_t per_step = world_ > 1 ? 7 : 3;  // gather, rhs, finish (+ wait, collect, halo push, state push)
+        int64_t per_step = world_ > 1 ? 5 : 3;  // gather, rhs, finish (+ state wait, collect)
         if (use_bicgstab()) {
             per_step += 1 + (int64_t)kBicgKernelsPerIter * b.trips;
         } else {
@@ -1237,7 +1290,7 @@ class SolverT final : public SolverBase {
                     cg_direction<R><<<g_vec_, kBlock, 0, stream_>>>(d_r_[0].p, d_p_[0].p, d_dinv0_.p, n_, d_st_, part_rr(), part_rz(), g_vec_, none, 0, one);
                     break;
                 default:
-                    launch_rhs(stream_, sc, part_rhs(), one);
+                    launch_rhs(stream_, sc, part_rhs(), one, 0);
                     break;
             }
         };
@@ -1381,6 +1434,7 @@ class SolverT final : public SolverBase {
         CK(cudaSetDevice(device_));
         CK(cudaStreamSynchronize(stream_));
         ls_stream_ = shared ? shared : stream_;
+        lockstep_ = true;
         ensure_operator_on(ls_stream_);
         return ls_stream_;
     }
@@ -1413,6 +1467,7 @@ class SolverT final : public SolverBase {
     int64_t ls_maxit() override { return maxit(); }
     void ls_finish_call(int nsteps) override {
         CK(cudaStreamSynchronize(ls_stream_));
+        lockstep_ = false;
         last_steps_ = nsteps;
         last_ms_ = 0;
         check_comm_error();
@@ -1484,11 +1539,11 @@ class SolverT final : public SolverBase {
     // persistent whole-solve kernel
     int pcg_max_grid_ = 0;
     int dual_max_grid_ = 0;
+    int grid_cap_ = INT32_MAX;
     bool dual_ = true;   // FEAB_DUAL=0 runs the two Gray-Scott solves one after the other
     bool dual_last_ = false;
     DevBuf<R> d_dpart_;
     bool rhs_tma_ = true;
-    unsigned long long* d_bar_ = nullptr;
     bool prof_dual_ = false;
     unsigned long long* d_prof_ = nullptr;  // FEAB_PCG_PROF=1: phase timers of the persistent kernel (CTA 0)
     DevBuf<R> d_ppart_;
@@ -1499,6 +1554,8 @@ class SolverT final : public SolverBase {
     double last_ms_ = 0;
     int64_t last_steps_ = 0;
     int64_t launches_ = 0;
+    bool values_dirty_ = true;            // surface->values was written by somebody other than finish_step since the last step
+    int step_stamp_ = 0, last_stamp_ = 0; // instability flag stamps (finish_step)
 };
 
 // ---------------------------------------------------------------- BiCGSTAB driver

@@ -31,10 +31,11 @@ struct PcgDualArgs {
     R* y[2];
     int64_t n;
     int num_tiles;
-    CgState<R>* st;           // [2], prepared by cg_begin
+    CgState<R>* st;           // [2]: written here (the start of both solves is taken from the RHS kernel's published sums)
     R* part;                  // 6 x gridDim.x: pap0 | pap1 | rr0 | rr1 | rz0 | rz1
-    unsigned long long* bar;  // zero at launch
     int first_halo_tile;      // partitioned: first tile with a row that reads a ghost column
+    R tol;
+    int maxit;
     unsigned long long* prof; // optional (FEAB_PCG_PROF=2): ns spent by CTA 0, same slots as PcgArgs::prof
 };
 
@@ -59,12 +60,25 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a, Com
     uint64_t* full = reinterpret_cast<uint64_t*>(base + Cfg::kStageBytes * STAGES);
     __shared__ R red[(NWT + 1) * 4];
     __shared__ double s_v[kMaxRanks * 4];
+    __shared__ int s_ctl[2];
 
-    if (a.st[0].done || a.st[1].done) return;  // cg_begin settled one of them: the single-system kernels take over (uniform)
-    R thr[2] = {a.st[0].thr, a.st[1].thr};
-    const int maxit = min(a.st[0].maxit, a.st[1].maxit);
-    R abs_old[2] = {a.st[0].abs_new[0], a.st[1].abs_new[0]};
+    if (comm_failed(cm)) return;  // an earlier kernel of this call lost a peer: fail closed
+    if (threadIdx.x == 0) s_ctl[1] = 0;
+    unsigned long long ar_seq = *(volatile unsigned long long*)&cm.loc->ar_seq;
+    unsigned long long halo_seq = *(volatile unsigned long long*)&cm.loc->halo_seq;
+    unsigned long long bar_seq = ld_volatile_u64(&cm.loc->gs_release);
+    __syncthreads();
     const int64_t n = a.n;
+    CgState<R> c2[2];
+    if (!pcg_begin<R, 2>(cm, ar_seq, a.tol, a.maxit, a.st, c2, s_v, s_ctl)) return;
+    if (c2[0].done || c2[1].done) {  // one solve ended before it began: the single-system kernel takes the other one (uniform)
+        for (int s = 0; s < 2; s++)
+            if (c2[s].done) zero_solution<R>(a.x[s], n);
+        return;
+    }
+    R thr[2] = {c2[0].thr, c2[1].thr};
+    const int maxit = a.maxit;
+    R abs_old[2] = {c2[0].abs_new[0], c2[1].abs_new[0]};
     const int num_tiles = a.num_tiles;
     const int h = (int)threadIdx.x / ROWS;   // which system this thread multiplies
     const int t = (int)threadIdx.x % ROWS;   // its row inside the tile
@@ -105,12 +119,6 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a, Com
     };
     prologue();
 
-    unsigned long long bar_target = 0;
-    unsigned long long ar_seq = 0, halo_seq = 0;
-    if (cm.world > 1) {
-        ar_seq = *(volatile unsigned long long*)&cm.loc->ar_seq;
-        halo_seq = *(volatile unsigned long long*)&cm.loc->halo_seq;
-    }
     // partitioned solve: mirror a boundary row's new p_s on every neighbour that keeps it as a ghost
     auto push_row = [&](int sys, int64_t row, R val) {
         if (row < hp.n_int) return;
@@ -131,8 +139,9 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a, Com
     R* const ph = a.p[h];
     R* const yh = a.y[h];
 
-    int it = a.st[0].iter1;
+    int it = 0;
     const int it0 = it;
+    bool failed = false;
     int iters[2] = {0, 0};
     bool fin[2] = {false, false};
     R rr[2] = {(R)0, (R)0};
@@ -151,7 +160,7 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a, Com
         int k = 0;
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, k++) {
             if (!halo_ok && tile >= a.first_halo_tile) {  // both directions' ghosts arrive under one flag value
-                if (threadIdx.x == 0) wait_flags(cm, hp, 0, halo_seq);
+                if (threadIdx.x == 0 && !wait_flags(cm, hp, 0, halo_seq)) s_ctl[1] = 1;
                 __syncthreads();
                 halo_ok = true;
             }
@@ -231,20 +240,20 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a, Com
         acc = warp_sum(acc);
         if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
         __syncthreads();
-        if (threadIdx.x < 2) {
-            R s = (R)0;
-            for (int w = 0; w < NWH; w++) s += red[threadIdx.x * NWH + w];
-            part[(size_t)threadIdx.x * G + blockIdx.x] = s;
+        R pap[2] = {(R)0, (R)0};
+        if (threadIdx.x == 0) {
+#pragma unroll
+            for (int s = 0; s < 2; s++)
+                for (int w = 0; w < NWH; w++) pap[s] += red[s * NWH + w];
         }
         __syncthreads();
         prologue();
         DUAL_STAMP(0)
-        grid_barrier(a.bar, bar_target);
-        R pap[2];
-        sum_cta_partials_vec<R, 2, NWT>(part, (size_t)G, pap, red);
+        if (!gsync_allreduce<R, 2, NWT>(cm, ar_seq, part, pap, red, s_v, s_ctl)) {
+            failed = true;
+            break;
+        }
         DUAL_STAMP(1)
-        if (cm.world > 1) ar_exchange<R, 2>(cm, ar_seq, pap, s_v);
-        DUAL_STAMP(2)
 
         // ---------------- phase B (both systems): r -= alpha y, |r|^2, r.z ----------------
         R alpha[2];
@@ -283,24 +292,18 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a, Com
             pb[2 + s] = prz;
         }
         block_sum_vec<R, 4, NWT>(pb, red);
-        if (threadIdx.x == 0) {
-#pragma unroll
-            for (int k = 0; k < 4; k++) part[(size_t)(2 + k) * G + blockIdx.x] = pb[k];
-        }
         DUAL_STAMP(3)
-        grid_barrier(a.bar, bar_target);
-        R rz[2];
-        {
-            R t4[4];
-            sum_cta_partials_vec<R, 4, NWT>(part + (size_t)2 * G, (size_t)G, t4, red);
-            DUAL_STAMP(4)
-            if (cm.world > 1) ar_exchange<R, 4>(cm, ar_seq, t4, s_v);
-            DUAL_STAMP(5)
-            rr[0] = t4[0];
-            rr[1] = t4[1];
-            rz[0] = t4[2];
-            rz[1] = t4[3];
+        if (!gsync_allreduce<R, 4, NWT>(cm, ar_seq, part + (size_t)2 * G, pb, red, s_v, s_ctl)) {
+            failed = true;
+            break;
         }
+        DUAL_STAMP(4)
+        R rz[2];
+        rr[0] = pb[0];
+        rr[1] = pb[1];
+        rz[0] = pb[2];
+        rz[1] = pb[3];
+        const bool first = it == 1;  // x0 = 0 is never stored: the first update writes 0 + alpha p
         bool pushed = false;
         // ---------------- stopping tests (ConjugateGradient.h:72-73), per system; direction update for the ones that go on ----
 #pragma unroll
@@ -314,14 +317,19 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a, Com
                 if (!conv) abs_old[s] = rz[s];
                 for (int64_t i = gtid; i < nvec; i += gthreads) {  // the deferred x += alpha p of the last iteration
                     R xv[N], pv[N];
-                    vload_cs<R>(xs + i * N, xv);
+                    if (first) {
+#pragma unroll
+                        for (int q = 0; q < N; q++) xv[q] = (R)0;
+                    } else {
+                        vload_cs<R>(xs + i * N, xv);
+                    }
                     vload<R>(ps + i * N, pv);
 #pragma unroll
                     for (int q = 0; q < N; q++) xv[q] = O::add(xv[q], O::mul(alpha[s], pv[q]));
                     vstore_cs<R>(xs + i * N, xv);
                 }
                 if (blockIdx.x == 0)
-                    for (int64_t i = nvec * N + threadIdx.x; i < n; i += blockDim.x) xs[i] = O::add(xs[i], O::mul(alpha[s], ps[i]));
+                    for (int64_t i = nvec * N + threadIdx.x; i < n; i += blockDim.x) xs[i] = O::add(first ? (R)0 : xs[i], O::mul(alpha[s], ps[i]));
             } else {
                 const R beta = rz[s] / abs_old[s];
                 abs_old[s] = rz[s];
@@ -329,7 +337,12 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a, Com
                 const R* const ds = a.dinv[s];
                 for (int64_t i = gtid; i < nvec; i += gthreads) {
                     R xv[N], rv[N], pv[N], dv[N];
-                    vload_cs<R>(xs + i * N, xv);
+                    if (first) {
+#pragma unroll
+                        for (int q = 0; q < N; q++) xv[q] = (R)0;
+                    } else {
+                        vload_cs<R>(xs + i * N, xv);
+                    }
                     vload<R>(rs + i * N, rv);
                     vload<R>(ps + i * N, pv);
                     vload<R>(ds + i * N, dv);
@@ -349,7 +362,7 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a, Com
                 if (blockIdx.x == 0)
                     for (int64_t i = nvec * N + threadIdx.x; i < n; i += blockDim.x) {
                         const R pi = ps[i];
-                        xs[i] = O::add(xs[i], O::mul(alpha[s], pi));
+                        xs[i] = O::add(first ? (R)0 : xs[i], O::mul(alpha[s], pi));
                         const R pn = O::add(O::mul(ds[i], rs[i]), O::mul(beta, pi));
                         ps[i] = pn;
                         if (cm.world > 1) {
@@ -363,20 +376,22 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a, Com
         if (fin[0] && fin[1]) break;
         if (cm.world == 1) {
             if (fin[0] || fin[1]) break;  // the kernel boundary is the barrier the survivor's next SpMV needs
-            grid_barrier(a.bar, bar_target);
+            if (!gsync_barrier(cm, hp, bar_seq, 0ull, s_ctl)) {
+                failed = true;
+                break;
+            }
             DUAL_STAMP(7)
         } else {
-            // same hand-shake as pcg_persistent.cuh: pushers fence, grid barrier, then one flag value covers both directions.
-            // A survivor's last push here is what its first SpMV in the single-system kernel waits for.
+            // same hand-shake as pcg_persistent.cuh: pushers fence, grid sync, the last CTA to arrive raises the flags; one
+            // flag value covers both directions.  A survivor's last push here is what its first SpMV in the single-system
+            // kernel waits for.
             if (__syncthreads_or(pushed ? 1 : 0)) __threadfence_system();
-            grid_barrier(a.bar, bar_target);
-            DUAL_STAMP(7)
             halo_seq += 1;
-            if (blockIdx.x == 0) {
-                if (threadIdx.x == 0) cm.loc->halo_seq = halo_seq;
-                if ((int)threadIdx.x < hp.nnb) st_relaxed_sys(&cm.ctrl[hp.nb_rank[threadIdx.x]]->halo_flag[cm.rank], halo_seq);
+            if (!gsync_barrier(cm, hp, bar_seq, halo_seq, s_ctl)) {
+                failed = true;
+                break;
             }
-            DUAL_STAMP(8)
+            DUAL_STAMP(7)
             if (fin[0] || fin[1]) break;
         }
     }
@@ -391,11 +406,12 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a, Com
         }
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) {
+        if (failed) cm.loc->error = 1;
         for (int s = 0; s < 2; s++) {
             CgState<R>* st = a.st + s;
             st->rn2 = rr[s];
             st->iter1 = it;
-            if (fin[s]) {
+            if (fin[s] || failed) {
                 st->abs_new[it & 1] = abs_old[s];
                 st->iters = iters[s];
                 st->done = 1;

@@ -4,15 +4,18 @@
 //   B  alpha; r -= alpha y; partials of |r|^2 and r.(D^-1 r)
 //   C  convergence test (every CTA takes the same decision from the same fixed-order sums), beta,
 //      x += alpha p (deferred from B: C reads p anyway), p = D^-1 r + beta p
-// separated by grid barriers instead of kernel boundaries.  What this buys:
+// separated by grid-wide syncs instead of kernel boundaries.  What this buys:
 //   * one GPU: no launch gaps, no graph WHILE node, and the TMA prologue of the next SpMV is issued before phases B/C
 //     so the matrix stream never drains;
-//   * partitioned solve: per iteration 2 mailbox all-reduces + 1 halo push ride on the barriers (CTA 0 publishes /
-//     pushes, every CTA consumes), instead of 4 kernel launches whose heads and tails wait for the peers.
+//   * partitioned solve: per iteration the 2 all-reduces ARE the two grid syncs (comm.cuh gsync_allreduce: the last CTA
+//     to arrive publishes the rank total to every rank's mailbox, every CTA waits on the mailbox) and the halo flags of
+//     the new direction are raised by the last CTA to arrive at the third.
+// The start of the solve (threshold, early-outs: ConjugateGradient.h:43-60) is taken inside the kernel from the sums the
+// RHS kernel published, and x = 0 is never written: the first iteration stores 0 + alpha p.  So a time step is
+// RHS kernel -> solve kernel(s) -> epilogue kernel, nothing else.
 // The arithmetic (operation order inside a row, per-CTA partials re-summed in CTA order) is the same as in the
 // three-kernel version.  Vectors that change during the kernel (p, r, x, y) are never read through the non-coherent
-// path; the barrier follows the fence / atomic / acquire pattern of cooperative groups, which also drops stale L1
-// lines.
+// path; the syncs follow the fence / atomic / fence pattern of cooperative groups, which also drops stale L1 lines.
 #pragma once
 #include "comm.cuh"
 #include "common.cuh"
@@ -21,99 +24,76 @@
 
 namespace feab {
 
-__device__ __forceinline__ unsigned long long ld_acquire_gpu_u64(const unsigned long long* p) {
-    unsigned long long v;
-    asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-    return v;
-}
-
-// Monotonic 64-bit arrival counter, zeroed by the host before every launch.  `target` is this thread's running count.
-__device__ __forceinline__ void grid_barrier(unsigned long long* counter, unsigned long long& target) {
-    __syncthreads();
-    target += gridDim.x;
-    if (threadIdx.x == 0) {
-        __threadfence();
-        atomicAdd(counter, 1ull);
-        while (ld_acquire_gpu_u64(counter) < target) {
-        }
-        __threadfence();
-    }
-    __syncthreads();
-}
-
 template <typename R>
 struct PcgArgs {
     const int* rowptr;
     const int* col;
-    const R* A;
-    const R* dinv;
-    R* x;
-    R* r;
-    R* p;
+    const R* A[2];    // per system (Gray-Scott has two; the others use [0])
+    const R* dinv[2];
+    R* x[2];
+    R* r[2];
+    R* p[2];
     R* y;
     int64_t n;
     int num_tiles;
     int first_halo_tile;
-    CgState<R>* st;          // prepared by cg_begin (threshold, r.z of the first direction, early-outs)
-    R* part;                 // 3 x gridDim.x: p.Ap | |r|^2 | r.z
-    unsigned long long* bar; // grid barrier counter (zero at launch)
-    int vec_p;               // which arena vector p is (kVecP0 / kVecP1): where the neighbours keep its ghosts
-    unsigned long long* prof; // optional (FEAB_PCG_PROF=1): ns spent by CTA 0 in [A, bar1+sum, ar1, B, bar2+sum, ar2, C, bar3, push], iterations
+    CgState<R>* st;    // [2]
+    R* part;           // 3 x gridDim.x: p.Ap | |r|^2 | r.z
+    int slot;          // >= 0: solve this system; -1: whichever of the two pcg_dual left running (the tail of a Gray-Scott step)
+    int begin;         // > 0: this is the first solve kernel of the step: number of systems (1 or 2) whose start is taken here
+                       // from the RHS kernel's published sums (mailbox all-reduce number ar_seq); 0: CgState is already set
+    R tol;
+    int maxit;
+    unsigned long long* prof; // optional (FEAB_PCG_PROF=1): ns spent by CTA 0 in [A, sync1 (barrier + all-reduce of p.Ap), -, B, sync2, -, C, sync3, -], iterations
 };
 
-// Sum of gridDim.x per-CTA partials written before the last grid barrier, in CTA order; identical in every CTA.
-template <typename R, int NW>
-__device__ __forceinline__ R sum_cta_partials(const R* part, R* red) {
-    R s = (R)0;
-    for (int i = threadIdx.x; i < (int)gridDim.x; i += blockDim.x) s += __ldcg(part + i);
-    s = block_sum_n<R, NW>(s, red);
-    __syncthreads();
-    return s;
-}
-
-// K such sums at once (partials of sum k at part + k * stride): one pass over L2, one block reduction; same bits.
-template <typename R, int K, int NW>
-__device__ __forceinline__ void sum_cta_partials_vec(const R* part, size_t stride, R (&out)[K], R* red /* (NW + 1) * K */) {
+// Start of the step's solves, ConjugateGradient.h:43-60 with x0 = 0 (IterativeSolverBase.h:357-360): residual = b, so
+// |b|^2 and b.D^-1 b are all that is needed; the RHS kernel's last CTA all-reduced them into the mailbox (all-reduce
+// number *seq, [2 s] = |b_s|^2, [2 s + 1] = b_s.D^-1 b_s).  Every CTA computes the same state; thread 0 of CTA 0 records it.
+template <typename R, int NS>
+__device__ __forceinline__ bool pcg_begin(const Comm& cm, unsigned long long seq, R tol, int maxit, CgState<R>* st_global, CgState<R> (&out)[NS],
+                                          double* s_pk, int* s_ctl) {
+    if ((int)threadIdx.x < cm.world) {
+        const ArSlot* mine = &cm.ctrl[cm.rank]->slot[seq & 1][threadIdx.x];
+        bool ok = true;
 #pragma unroll
-    for (int k = 0; k < K; k++) out[k] = (R)0;
-    for (int i = threadIdx.x; i < (int)gridDim.x; i += blockDim.x) {
-#pragma unroll
-        for (int k = 0; k < K; k++) out[k] += __ldcg(part + k * stride + i);
+        for (int k = 0; k < 2 * NS; k++) s_pk[threadIdx.x * 4 + k] = ll_wait(mine, k, seq, cm.loc, &ok, (int)threadIdx.x);
+        if (!ok) s_ctl[1] = 1;
+        __threadfence();
     }
-    block_sum_vec<R, K, NW>(out, red);
-}
-
-// Mailbox all-reduce riding on a grid barrier: CTA 0 stores the rank totals into every peer's mailbox (one thread per
-// peer, LL words: no fence), every CTA waits for the peers' totals in its own mailbox (one thread per peer) and adds
-// them in rank order -- bit-identical on all CTAs of all ranks.
-template <typename R, int K>
-__device__ __forceinline__ void ar_exchange(const Comm& cm, unsigned long long& seq, R (&v)[K], double* s_pk /* kMaxRanks * 4 */) {
-    seq += 1;
-    const int q = threadIdx.x;
-    if (q < cm.world) {
-        if (q == cm.rank) {
-            if (blockIdx.x == 0) cm.loc->ar_seq = seq;
+    __syncthreads();
 #pragma unroll
-            for (int k = 0; k < K; k++) s_pk[q * 4 + k] = (double)v[k];
-        } else {
-            if (blockIdx.x == 0) {
-                ArSlot* sl = &cm.ctrl[q]->slot[seq & 1][cm.rank];
-#pragma unroll
-                for (int k = 0; k < K; k++) ll_store(sl, k, (double)v[k], seq);
-            }
-            const ArSlot* mine = &cm.ctrl[cm.rank]->slot[seq & 1][q];
-#pragma unroll
-            for (int k = 0; k < K; k++) s_pk[q * 4 + k] = ll_wait(mine, k, seq, cm.loc);
+    for (int s = 0; s < NS; s++) {
+        R bb = (R)0, rz = (R)0;
+        for (int w = 0; w < cm.world; w++) {
+            bb += (R)s_pk[w * 4 + 2 * s];
+            rz += (R)s_pk[w * 4 + 2 * s + 1];
         }
+        R thr = tol * tol * bb;
+        if (thr < Ops<R>::tiny()) thr = Ops<R>::tiny();
+        CgState<R>& c = out[s];
+        c.rhs2 = bb;
+        c.thr = thr;
+        c.rn2 = bb == (R)0 ? (R)0 : bb;
+        c.tol = tol;
+        c.abs_new[0] = rz;
+        c.abs_new[1] = (R)0;
+        c.iter1 = 0;
+        c.iters = 0;
+        c.maxit = maxit;
+        c.done = (bb == (R)0 || bb < thr || maxit <= 0) ? 1 : 0;
+        if (blockIdx.x == 0 && threadIdx.x == 0) st_global[s] = c;
     }
+    const bool failed = s_ctl[1] != 0;
     __syncthreads();
-#pragma unroll
-    for (int k = 0; k < K; k++) {
-        R acc = (R)0;
-        for (int w = 0; w < cm.world; w++) acc += (R)s_pk[w * 4 + k];
-        v[k] = acc;
-    }
-    __syncthreads();
+    return !failed;
+}
+
+// x = 0 for a system whose solve ended before its first iteration (rhs == 0: ConjugateGradient.h:45-49; residual already
+// below the threshold: x keeps the zero guess)
+template <typename R>
+__device__ __forceinline__ void zero_solution(R* x, int64_t n) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) x[i] = (R)0;
 }
 
 template <typename R, int ROWS, int CPR, int STAGES, int MINB>
@@ -125,16 +105,55 @@ __global__ void __launch_bounds__(ROWS, MINB) pcg_persistent(PcgArgs<R> a, Comm 
     unsigned char* base = reinterpret_cast<unsigned char*>(((uintptr_t)smraw_pcg + 127) & ~(uintptr_t)127);
     uint64_t* full = reinterpret_cast<uint64_t*>(base + Cfg::kStageBytes * STAGES);
     __shared__ R red[(NW + 1) * 2];
-    __shared__ double s_v[kMaxRanks * 4];
+    __shared__ double s_pk[kMaxRanks * 4];
+    __shared__ int s_ctl[2];
 
-    CgState<R>* st = a.st;
-    if (st->done) return;  // rhs == 0 or already below the threshold (cg_begin); uniform over the grid
-    const R thr = st->thr;
-    const int maxit = st->maxit;
-    R abs_old = st->abs_new[0];
+    if (comm_failed(cm)) return;  // an earlier kernel of this call lost a peer: fail closed
+    if (threadIdx.x == 0) s_ctl[1] = 0;
+    unsigned long long ar_seq = *(volatile unsigned long long*)&cm.loc->ar_seq;
+    unsigned long long halo_seq = *(volatile unsigned long long*)&cm.loc->halo_seq;
+    unsigned long long bar_seq = ld_volatile_u64(&cm.loc->gs_release);
+    __syncthreads();
+
+    // ---- which system, and its state ----
+    int slot = a.slot;
+    CgState<R> c;
+    if (a.begin > 0) {
+        CgState<R> b2[2];
+        bool ok;
+        if (a.begin == 2) {
+            ok = pcg_begin<R, 2>(cm, ar_seq, a.tol, a.maxit, a.st, b2, s_pk, s_ctl);
+        } else {
+            CgState<R> b1[1];
+            ok = pcg_begin<R, 1>(cm, ar_seq, a.tol, a.maxit, a.st, b1, s_pk, s_ctl);
+            b2[0] = b1[0];
+            b2[1] = b1[0];
+        }
+        if (!ok) return;
+        for (int s = 0; s < a.begin; s++)
+            if (b2[s].done) zero_solution<R>(a.x[s], a.n);
+        c = b2[slot];
+    } else {
+        if (slot < 0) {
+            const int d0 = a.st[0].done, d1 = a.st[1].done;
+            if (d0 && d1) return;
+            slot = d0 ? 1 : 0;
+        }
+        c = a.st[slot];
+    }
+    if (c.done) return;  // uniform over the grid
+    CgState<R>* st = a.st + slot;
+    const R* const Aval = a.A[slot];
+    const R* const dinv = a.dinv[slot];
+    R* const xs = a.x[slot];
+    R* const rs = a.r[slot];
+    R* const px = a.p[slot];  // the SpMV gathers from p: plain (coherent) loads only
+    const int vec_p = slot == 0 ? kVecP0 : kVecP1;
+    const R thr = c.thr;
+    const int maxit = c.maxit;
+    R abs_old = c.abs_new[0];
     const int64_t n = a.n;
     const int num_tiles = a.num_tiles;
-    R* const px = a.p;  // the SpMV gathers from p: plain (coherent) loads only
 
     auto stage_val = [&](int s) { return reinterpret_cast<R*>(base + (size_t)s * Cfg::kStageBytes); };
     auto stage_col = [&](int s) { return reinterpret_cast<int*>(base + (size_t)s * Cfg::kStageBytes + Cfg::kValBytes); };
@@ -160,7 +179,7 @@ __global__ void __launch_bounds__(ROWS, MINB) pcg_persistent(PcgArgs<R> a, Comm 
         mbar_expect_tx(&full[s], bytes);
         tma_load_1d(stage_rp(s), a.rowptr + r0, rp_b, &full[s], policy);
         if (staged) {
-            tma_load_1d(stage_val(s), a.A + tba, (uint32_t)cnt_al * (uint32_t)sizeof(R), &full[s], policy);
+            tma_load_1d(stage_val(s), Aval + tba, (uint32_t)cnt_al * (uint32_t)sizeof(R), &full[s], policy);
             tma_load_1d(stage_col(s), a.col + tba, (uint32_t)cnt_al * 4u, &full[s], policy);
         }
     };
@@ -175,15 +194,8 @@ __global__ void __launch_bounds__(ROWS, MINB) pcg_persistent(PcgArgs<R> a, Comm 
     };
     prologue();
 
-    unsigned long long bar_target = 0;
-    unsigned long long ar_seq = 0, halo_seq = 0;
-    if (cm.world > 1) {
-        ar_seq = *(volatile unsigned long long*)&cm.loc->ar_seq;
-        halo_seq = *(volatile unsigned long long*)&cm.loc->halo_seq;
-    }
     R* part_pap = a.part;
     R* part_rr = a.part + gridDim.x;
-    R* part_rz = a.part + 2 * (size_t)gridDim.x;
     constexpr int N = Vec<R>::N;
     const int64_t nvec = n / N;
     const int64_t gthreads = (int64_t)gridDim.x * blockDim.x;
@@ -195,18 +207,19 @@ __global__ void __launch_bounds__(ROWS, MINB) pcg_persistent(PcgArgs<R> a, Comm 
         const int* t = hp.push_tab + (size_t)(row - hp.n_int) * hp.nnb;
         for (int b = 0; b < hp.nnb; b++) {
             const int d = t[b];
-            if (d >= 0) reinterpret_cast<R*>(hp.base[hp.nb_rank[b]] + hp.off_vec[a.vec_p][hp.nb_rank[b]])[d] = val;
+            if (d >= 0) reinterpret_cast<R*>(hp.base[hp.nb_rank[b]] + hp.off_vec[vec_p][hp.nb_rank[b]])[d] = val;
         }
     };
-    int it = st->iter1, iters = 0;  // 0 after cg_begin; pcg_dual.cuh hands a running solve over with its count
+    int it = c.iter1, iters = 0;  // 0 at the start of a solve; pcg_dual.cuh hands a running solve over with its count
     const int it0 = it;
-    R rr = (R)0;
+    R rr = c.rn2;
+    bool failed = false;
     const bool prof = a.prof != nullptr && blockIdx.x == 0 && threadIdx.x == 0;
     unsigned long long t_last = prof ? globaltimer_ns() : 0ull;
-#define PCG_STAMP(slot)                               \
+#define PCG_STAMP(slot_)                              \
     if (prof) {                                       \
         const unsigned long long t_now = globaltimer_ns(); \
-        a.prof[slot] += t_now - t_last;               \
+        a.prof[slot_] += t_now - t_last;              \
         t_last = t_now;                               \
     }
     while (true) {
@@ -216,7 +229,7 @@ __global__ void __launch_bounds__(ROWS, MINB) pcg_persistent(PcgArgs<R> a, Comm 
         int k = 0;
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, k++) {
             if (!halo_ok && tile >= a.first_halo_tile) {
-                if (threadIdx.x == 0) wait_flags(cm, hp, 0, halo_seq);
+                if (threadIdx.x == 0 && !wait_flags(cm, hp, 0, halo_seq)) s_ctl[1] = 1;
                 __syncthreads();
                 halo_ok = true;
             }
@@ -274,10 +287,10 @@ __global__ void __launch_bounds__(ROWS, MINB) pcg_persistent(PcgArgs<R> a, Comm 
                 } else {
                     int q = kb;
                     for (; q + 1 < ke; q += 2) {
-                        ta += a.A[q] * px[a.col[q]];
-                        tb2 += a.A[q + 1] * px[a.col[q + 1]];
+                        ta += Aval[q] * px[a.col[q]];
+                        tb2 += Aval[q + 1] * px[a.col[q + 1]];
                     }
-                    if (q < ke) ta += a.A[q] * px[a.col[q]];
+                    if (q < ke) ta += Aval[q] * px[a.col[q]];
                     xr = px[r];
                 }
                 const R sum = ta + tb2;
@@ -292,16 +305,15 @@ __global__ void __launch_bounds__(ROWS, MINB) pcg_persistent(PcgArgs<R> a, Comm 
         }
         fills += (unsigned)k;
         it++;
-        acc = block_sum_n<R, NW>(acc, red);
-        if (threadIdx.x == 0) part_pap[blockIdx.x] = acc;
+        R pap[1] = {block_sum_n<R, NW>(acc, red)};
         __syncthreads();
         prologue();  // next iteration's first tiles stream in while phases B / C run
         PCG_STAMP(0)
-        grid_barrier(a.bar, bar_target);
-        R pap[1] = {sum_cta_partials<R, NW>(part_pap, red)};
+        if (!gsync_allreduce<R, 1, NW>(cm, ar_seq, part_pap, pap, red, s_pk, s_ctl)) {
+            failed = true;
+            break;
+        }
         PCG_STAMP(1)
-        if (cm.world > 1) ar_exchange<R, 1>(cm, ar_seq, pap, s_v);
-        PCG_STAMP(2)
 
         // ---------------- phase B: r -= alpha y, |r|^2, r.z  (ConjugateGradient.h:67-76) --------------------------
         // x += alpha p is deferred to phase C, which reads p anyway (one vector read less per iteration; same
@@ -310,9 +322,9 @@ __global__ void __launch_bounds__(ROWS, MINB) pcg_persistent(PcgArgs<R> a, Comm 
         R prr = (R)0, prz = (R)0;
         for (int64_t i = gtid; i < nvec; i += gthreads) {
             R rv[N], yv[N], dv[N];
-            vload<R>(a.r + i * N, rv);
+            vload<R>(rs + i * N, rv);
             vload<R>(a.y + i * N, yv);
-            vload<R>(a.dinv + i * N, dv);
+            vload<R>(dinv + i * N, dv);
 #pragma unroll
             for (int q = 0; q < N; q++) {
                 rv[q] = O::sub(rv[q], O::mul(alpha, yv[q]));
@@ -320,34 +332,28 @@ __global__ void __launch_bounds__(ROWS, MINB) pcg_persistent(PcgArgs<R> a, Comm 
                 prr += rv[q] * rv[q];
                 prz += rv[q] * z;
             }
-            vstore<R>(a.r + i * N, rv);
+            vstore<R>(rs + i * N, rv);
         }
         if (blockIdx.x == 0) {
             for (int64_t i = nvec * N + threadIdx.x; i < n; i += blockDim.x) {
-                R rn = O::sub(a.r[i], O::mul(alpha, a.y[i]));
-                a.r[i] = rn;
-                R z = O::mul(a.dinv[i], rn);
+                R rn = O::sub(rs[i], O::mul(alpha, a.y[i]));
+                rs[i] = rn;
+                R z = O::mul(dinv[i], rn);
                 prr += rn * rn;
                 prz += rn * z;
             }
         }
-        {
-            R pr2[2] = {prr, prz};
-            block_sum_vec<R, 2, NW>(pr2, red);
-            if (threadIdx.x == 0) {
-                part_rr[blockIdx.x] = pr2[0];
-                part_rz[blockIdx.x] = pr2[1];
-            }
-        }
+        R t2[2] = {prr, prz};
+        block_sum_vec<R, 2, NW>(t2, red);
         PCG_STAMP(3)
-        grid_barrier(a.bar, bar_target);
-        R t2[2];
-        sum_cta_partials_vec<R, 2, NW>(part_rr, (size_t)gridDim.x, t2, red);  // part_rz = part_rr + gridDim.x
+        if (!gsync_allreduce<R, 2, NW>(cm, ar_seq, part_rr, t2, red, s_pk, s_ctl)) {  // part_rz = part_rr + gridDim.x
+            failed = true;
+            break;
+        }
         PCG_STAMP(4)
-        if (cm.world > 1) ar_exchange<R, 2>(cm, ar_seq, t2, s_v);
-        PCG_STAMP(5)
         rr = t2[0];
         const R rz = t2[1];
+        const bool first = it == 1;  // x0 = 0 is never stored: the first update writes 0 + alpha p (same bits as x += alpha p on zeros)
 
         // ---------------- convergence test: same sums, same decision in every CTA (ConjugateGradient.h:72-73) -----
         const bool conv = rr < thr;
@@ -357,14 +363,19 @@ __global__ void __launch_bounds__(ROWS, MINB) pcg_persistent(PcgArgs<R> a, Comm 
             // the deferred x += alpha p of this last iteration
             for (int64_t i = gtid; i < nvec; i += gthreads) {
                 R xv[N], pv[N];
-                vload<R>(a.x + i * N, xv);
-                vload<R>(a.p + i * N, pv);
+                if (first) {
+#pragma unroll
+                    for (int q = 0; q < N; q++) xv[q] = (R)0;
+                } else {
+                    vload<R>(xs + i * N, xv);
+                }
+                vload<R>(px + i * N, pv);
 #pragma unroll
                 for (int q = 0; q < N; q++) xv[q] = O::add(xv[q], O::mul(alpha, pv[q]));
-                vstore<R>(a.x + i * N, xv);
+                vstore<R>(xs + i * N, xv);
             }
             if (blockIdx.x == 0)
-                for (int64_t i = nvec * N + threadIdx.x; i < n; i += blockDim.x) a.x[i] = O::add(a.x[i], O::mul(alpha, a.p[i]));
+                for (int64_t i = nvec * N + threadIdx.x; i < n; i += blockDim.x) xs[i] = O::add(first ? (R)0 : xs[i], O::mul(alpha, px[i]));
             break;
         }
         // ---------------- phase C: x += alpha p; p = D^-1 r + beta p  (ConjugateGradient.h:68, :77-80) -----------
@@ -373,17 +384,22 @@ __global__ void __launch_bounds__(ROWS, MINB) pcg_persistent(PcgArgs<R> a, Comm 
         bool pushed = false;
         for (int64_t i = gtid; i < nvec; i += gthreads) {
             R xv[N], rv[N], pv[N], dv[N];
-            vload<R>(a.x + i * N, xv);
-            vload<R>(a.r + i * N, rv);
-            vload<R>(a.p + i * N, pv);
-            vload<R>(a.dinv + i * N, dv);
+            if (first) {
+#pragma unroll
+                for (int q = 0; q < N; q++) xv[q] = (R)0;
+            } else {
+                vload<R>(xs + i * N, xv);
+            }
+            vload<R>(rs + i * N, rv);
+            vload<R>(px + i * N, pv);
+            vload<R>(dinv + i * N, dv);
 #pragma unroll
             for (int q = 0; q < N; q++) {
                 xv[q] = O::add(xv[q], O::mul(alpha, pv[q]));
                 pv[q] = O::add(O::mul(dv[q], rv[q]), O::mul(beta, pv[q]));
             }
-            vstore<R>(a.x + i * N, xv);
-            vstore<R>(a.p + i * N, pv);
+            vstore<R>(xs + i * N, xv);
+            vstore<R>(px + i * N, pv);
             if (cm.world > 1 && i * N + N > hp.n_int) {  // boundary rows: straight into the neighbours' ghost tails
 #pragma unroll
                 for (int q = 0; q < N; q++) push_row(i * N + q, pv[q]);
@@ -392,31 +408,25 @@ __global__ void __launch_bounds__(ROWS, MINB) pcg_persistent(PcgArgs<R> a, Comm 
         }
         if (blockIdx.x == 0)
             for (int64_t i = nvec * N + threadIdx.x; i < n; i += blockDim.x) {
-                const R pi = a.p[i];
-                a.x[i] = O::add(a.x[i], O::mul(alpha, pi));
-                const R pn = O::add(O::mul(a.dinv[i], a.r[i]), O::mul(beta, pi));
-                a.p[i] = pn;
+                const R pi = px[i];
+                xs[i] = O::add(first ? (R)0 : xs[i], O::mul(alpha, pi));
+                const R pn = O::add(O::mul(dinv[i], rs[i]), O::mul(beta, pi));
+                px[i] = pn;
                 if (cm.world > 1) {
                     push_row(i, pn);
                     pushed = true;
                 }
             }
-        if (cm.world > 1 && __syncthreads_or(pushed ? 1 : 0)) __threadfence_system();  // remote stores done before the barrier
+        // remote stores are complete system-wide before this CTA arrives at the sync; the last CTA to arrive then raises the
+        // neighbours' halo flags with release stores (comm.cuh gsync_barrier)
+        if (cm.world > 1 && __syncthreads_or(pushed ? 1 : 0)) __threadfence_system();
         PCG_STAMP(6)
-        grid_barrier(a.bar, bar_target);
-        PCG_STAMP(7)
-        if (cm.world > 1) {
-            // every boundary row of the new direction already sits in its neighbours' ghost tails: the CTAs that
-            // pushed ran a system-scope fence before arriving at the barrier, so the data is visible system-wide
-            // and a relaxed flag store is enough (a release here would cost another system fence on the critical path).  Every CTA counts the push so that its next halo wait
-            // asks for the right flag value.
-            halo_seq += 1;
-            if (blockIdx.x == 0) {  // one thread per neighbour: the flag stores leave in parallel
-                if (threadIdx.x == 0) cm.loc->halo_seq = halo_seq;
-                if ((int)threadIdx.x < hp.nnb) st_relaxed_sys(&cm.ctrl[hp.nb_rank[threadIdx.x]]->halo_flag[cm.rank], halo_seq);
-            }
+        halo_seq += 1;
+        if (!gsync_barrier(cm, hp, bar_seq, cm.world > 1 ? halo_seq : 0ull, s_ctl)) {
+            failed = true;
+            break;
         }
-        PCG_STAMP(8)
+        PCG_STAMP(7)
     }
 #undef PCG_STAMP
     if (prof) a.prof[9] += (unsigned long long)(it - it0);
@@ -432,8 +442,9 @@ __global__ void __launch_bounds__(ROWS, MINB) pcg_persistent(PcgArgs<R> a, Comm 
         st->rn2 = rr;
         st->abs_new[it & 1] = abs_old;
         st->iter1 = it;
-        st->iters = iters;
+        st->iters = failed ? it : iters;
         st->done = 1;
+        if (failed) cm.loc->error = 1;
     }
 }
 

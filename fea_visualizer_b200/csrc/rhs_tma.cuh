@@ -15,7 +15,7 @@ __global__ void __launch_bounds__(ROWS, MINB)
     rhs_init_tma(const int* __restrict__ rowptr, const int* __restrict__ col, const R* __restrict__ Md, const R* __restrict__ u,
                  const R* __restrict__ v, const R* __restrict__ dinv0, const R* __restrict__ dinv1, int64_t n, int num_tiles,
                  StepScalars sc, R* __restrict__ r0o, R* __restrict__ p0o, R* __restrict__ r1o, R* __restrict__ p1o,
-                 R* __restrict__ part /* 4 x pstride: bb0, rz0, bb1, rz1 */, int pstride, Comm cm) {
+                 R* __restrict__ part /* 4 x pstride: bb0, rz0, bb1, rz1 */, int pstride, Comm cm, HaloPlan hp, int publish) {
     static_assert(EQ == 0 || EQ == 2 || EQ == 3, "wave keeps rhs_init");
     using O = Ops<R>;
     using Cfg = TmaCfg<R, ROWS, CPR, STAGES>;
@@ -28,6 +28,7 @@ __global__ void __launch_bounds__(ROWS, MINB)
     auto stage_col = [&](int s) { return reinterpret_cast<int*>(base + (size_t)s * Cfg::kStageBytes + Cfg::kValBytes); };
     auto stage_rp = [&](int s) { return reinterpret_cast<int*>(base + (size_t)s * Cfg::kStageBytes + Cfg::kValBytes + Cfg::kColBytes); };
 
+    if (cm.world > 1 && comm_failed(cm)) return;  // fail closed (comm.cuh)
     uint64_t policy = 0;
     if (threadIdx.x == 0) {
         for (int s = 0; s < STAGES; s++) mbar_init(&full[s], 1);
@@ -54,6 +55,15 @@ __global__ void __launch_bounds__(ROWS, MINB)
         int t = blockIdx.x;
         for (int s = 0; s < STAGES && t < num_tiles; s++, t += gridDim.x) issue(t, s);
     }
+    // the matrix stream is on its way; the ghost entries of u / v come from the neighbours' end-of-step pushes
+    bool pushed = false;
+    if (cm.world > 1) {
+        if (threadIdx.x == 0) wait_flags(cm, hp, 1, *(volatile unsigned long long*)&cm.loc->state_seq);
+        __syncthreads();
+    }
+    // the vector surface->values feeds (u; Gray-Scott: v) is read through float (solver.cuh through_float)
+    auto ldu = [&](int64_t c) { return EQ == 3 ? u[c] : through_float(u[c]); };
+    auto ldv = [&](int64_t c) { return through_float(v[c]); };
 
     R bb0 = (R)0, rz0 = (R)0, bb1 = (R)0, rz1 = (R)0;
     int i = 0;
@@ -84,8 +94,8 @@ __global__ void __launch_bounds__(ROWS, MINB)
                 }
 #pragma unroll
                 for (int j = 0; j < 8; j++) {
-                    uv[j] = u[cv[j]];
-                    if (EQ == 3) vv[j] = v[cv[j]];
+                    uv[j] = ldu(cv[j]);
+                    if (EQ == 3) vv[j] = ldv(cv[j]);
                 }
 #pragma unroll
                 for (int j = 0; j < 8; j++) {
@@ -97,23 +107,23 @@ __global__ void __launch_bounds__(ROWS, MINB)
                 ui = uv[7];
                 if (EQ == 3) vi = vv[7];
                 if (len >= 8) {
-                    ui = u[r];
-                    if (EQ == 3) vi = v[r];
+                    ui = ldu(r);
+                    if (EQ == 3) vi = ldv(r);
                     for (int j = 8; j < len; j++) {
                         const int c = scl[j];
-                        s0 = O::add(s0, O::mul(sv[j], u[c]));
-                        if (EQ == 3) s1 = O::add(s1, O::mul(sv[j], v[c]));
+                        s0 = O::add(s0, O::mul(sv[j], ldu(c)));
+                        if (EQ == 3) s1 = O::add(s1, O::mul(sv[j], ldv(c)));
                     }
                 }
             } else {
                 for (int k = kb; k < ke; k++) {
                     const int c = col[k];
                     const R m = Md[k];
-                    s0 = O::add(s0, O::mul(m, u[c]));
-                    if (EQ == 3) s1 = O::add(s1, O::mul(m, v[c]));
+                    s0 = O::add(s0, O::mul(m, ldu(c)));
+                    if (EQ == 3) s1 = O::add(s1, O::mul(m, ldv(c)));
                 }
-                ui = u[r];
-                if (EQ == 3) vi = v[r];
+                ui = ldu(r);
+                if (EQ == 3) vi = ldv(r);
             }
             if (EQ == 3) {
                 const R f = (R)sc.c2, fk = O::add((R)sc.c2, (R)sc.c3);
@@ -129,12 +139,21 @@ __global__ void __launch_bounds__(ROWS, MINB)
                 rz0 += bu * pu;
                 bb1 += bv * bv;
                 rz1 += bv * pv;
+                if (cm.world > 1 && r >= hp.n_int) {  // first search directions of the boundary rows -> neighbours' ghost tails
+                    push_boundary_row<R>(hp, kVecP0, r, pu);
+                    push_boundary_row<R>(hp, kVecP1, r, pv);
+                    pushed = true;
+                }
             } else {
                 const R pz = O::mul(dinv0[r], s0);
                 r0o[r] = s0;
                 p0o[r] = pz;
                 bb0 += s0 * s0;
                 rz0 += s0 * pz;
+                if (cm.world > 1 && r >= hp.n_int) {
+                    push_boundary_row<R>(hp, kVecP0, r, pz);
+                    pushed = true;
+                }
             }
         }
         __syncthreads();  // every consumer is done with stage s
@@ -166,9 +185,10 @@ __global__ void __launch_bounds__(ROWS, MINB)
     if (blockIdx.x == 0)
         for (int k = 0; k < K; k++)
             for (int q = (int)gridDim.x + (int)threadIdx.x; q < pstride; q += ROWS) part[(size_t)k * pstride + q] = (R)0;
-    if (cm.world > 1) {
+    if (publish) {  // totals -> every rank's mailbox (persistent solve kernels and partitioned handles start from there)
+        if (cm.world > 1 && __syncthreads_or(pushed ? 1 : 0)) __threadfence_system();
         __syncthreads();
-        ar_publish<R, K, NW>(cm, part, pstride, red);
+        ar_publish<R, K, NW>(cm, part, pstride, red, &hp, cm.world > 1);
     }
 }
 

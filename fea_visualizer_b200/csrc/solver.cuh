@@ -42,8 +42,20 @@ __device__ __forceinline__ R ld_stream(const R* p) {
 // ------------------------------------------------------------------------------------------------
 // CPUSolver::get_surface_value_vector (src/FEM/CPUSolver.cpp:13-21)
 // ------------------------------------------------------------------------------------------------
+// surface->values is float: the vector it feeds passes through float once per step.  Between steps the solver keeps its
+// own (unrounded) solution and the RHS kernels apply this rounding when they read it, so gather_values only has to run when
+// somebody else wrote values (brush, set_values, host upload); same bits either way.
 template <typename R>
-__global__ void gather_values(const float* __restrict__ values, const int* __restrict__ colmap, int64_t V, R* __restrict__ x) {
+__device__ __forceinline__ R through_float(R x) {
+    return (R)(float)x;
+}
+
+template <typename R>
+__global__ void gather_values(const float* __restrict__ values, const int* __restrict__ colmap, int64_t V, R* __restrict__ x, Comm cm,
+                              HaloPlan hp) {
+    // partitioned: the ghost entries of values come from the neighbours' end-of-step pushes; the caller launches
+    // wait_kernel(state) first (one CTA spins, not V / 256 of them)
+    if (cm.world > 1 && comm_failed(cm)) return;
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < V) {
         int m = colmap[i];  // idx_map on one GPU; owned + ghost columns on a partition
@@ -430,7 +442,8 @@ __global__ void __launch_bounds__(kBlock) rhs_init(const int* __restrict__ rowpt
                                                    const R* __restrict__ v, const R* __restrict__ dinv0,
                                                    const R* __restrict__ dinv1, int64_t n, int num_tiles, StepScalars sc,
                                                    R* __restrict__ r0, R* __restrict__ p0, R* __restrict__ r1, R* __restrict__ p1,
-                                                   R* __restrict__ part /* 4 x gridDim.x: bb0, rz0, bb1, rz1 */, Comm cm) {
+                                                   R* __restrict__ part /* 4 x gridDim.x: bb0, rz0, bb1, rz1 */, Comm cm, HaloPlan hp,
+                                                   int publish) {
     using O = Ops<R>;
     extern __shared__ __align__(16) unsigned char smraw[];
     R* prod0 = reinterpret_cast<R*>(smraw);
@@ -439,20 +452,30 @@ __global__ void __launch_bounds__(kBlock) rhs_init(const int* __restrict__ rowpt
     __shared__ R red[kBlock / 32 + 1];
     R bb0 = (R)0, rz0 = (R)0, bb1 = (R)0, rz1 = (R)0;
     const R cc = O::mul((R)sc.c0, (R)sc.c0);
+    bool pushed = false;
+    if (cm.world > 1) {  // ghost entries of u / v come from the neighbours' end-of-step pushes
+        if (comm_failed(cm)) return;
+        if (threadIdx.x == 0) wait_flags(cm, hp, 1, *(volatile unsigned long long*)&cm.loc->state_seq);
+        __syncthreads();
+        if (comm_failed(cm)) return;
+    }
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         TileRange t = tile_range(rowptr, n, tile, s_k);
         const int cnt = t.te - t.tb;
         int64_t r = (int64_t)tile * kTileRows + threadIdx.x;
         R s0 = (R)0, s1 = (R)0;
         if (cnt <= kTileCap) {
+            // the vector surface->values feeds (u; Gray-Scott: v) is read through float (see through_float)
             if (EQ == 0 || EQ == 2) {
-                stage_products<R>(Md, col, u, t.tb, cnt, prod0);
+#pragma unroll 4
+                for (int i = threadIdx.x; i < cnt; i += kBlock)
+                    prod0[i] = ld_stream(Md + t.tb + i) * through_float(u[ld_stream(col + t.tb + i)]);
             } else if (EQ == 1) {
 #pragma unroll 4
                 for (int i = threadIdx.x; i < cnt; i += kBlock) {
                     int c = ld_stream(col + t.tb + i);
                     prod0[i] = ld_stream(Md + t.tb + i) * v[c];
-                    prod1[i] = O::mul(cc, ld_stream(Kv + t.tb + i)) * O::mul((R)-1, u[c]);
+                    prod1[i] = O::mul(cc, ld_stream(Kv + t.tb + i)) * O::mul((R)-1, through_float(u[c]));
                 }
             } else {
 #pragma unroll 4
@@ -460,7 +483,7 @@ __global__ void __launch_bounds__(kBlock) rhs_init(const int* __restrict__ rowpt
                     int c = ld_stream(col + t.tb + i);
                     R m = ld_stream(Md + t.tb + i);
                     prod0[i] = m * u[c];
-                    prod1[i] = m * v[c];
+                    prod1[i] = m * through_float(v[c]);
                 }
             }
             __syncthreads();
@@ -470,20 +493,20 @@ __global__ void __launch_bounds__(kBlock) rhs_init(const int* __restrict__ rowpt
         } else {
             for (int k = t.kb; k < t.ke; k++) {
                 int c = col[k];
-                if (EQ == 0 || EQ == 2) s0 += Md[k] * u[c];
+                if (EQ == 0 || EQ == 2) s0 += Md[k] * through_float(u[c]);
                 if (EQ == 1) s0 += Md[k] * v[c];
                 if (EQ == 3) {
                     s0 += Md[k] * u[c];
-                    s1 += Md[k] * v[c];
+                    s1 += Md[k] * through_float(v[c]);
                 }
             }
             if (EQ == 1)
-                for (int k = t.kb; k < t.ke; k++) s0 += O::mul(cc, Kv[k]) * O::mul((R)-1, u[col[k]]);
+                for (int k = t.kb; k < t.ke; k++) s0 += O::mul(cc, Kv[k]) * O::mul((R)-1, through_float(u[col[k]]));
         }
         if (r < n) {
             if (EQ == 3) {
                 const R f = (R)sc.c2, fk = O::add((R)sc.c2, (R)sc.c3);
-                R ui = u[r], vi = v[r];
+                R ui = u[r], vi = through_float(v[r]);
                 R uvv = O::mul(ui, O::mul(vi, vi));
                 R bu = O::add(O::sub(s0, uvv), O::mul(f, O::sub((R)1, ui)));
                 R bv = O::sub(O::add(s1, uvv), O::mul(fk, vi));
@@ -496,12 +519,21 @@ __global__ void __launch_bounds__(kBlock) rhs_init(const int* __restrict__ rowpt
                 rz0 += bu * pu;
                 bb1 += bv * bv;
                 rz1 += bv * pv;
+                if (cm.world > 1 && r >= hp.n_int) {  // first search directions of the boundary rows -> neighbours' ghost tails
+                    push_boundary_row<R>(hp, kVecP0, r, pu);
+                    push_boundary_row<R>(hp, kVecP1, r, pv);
+                    pushed = true;
+                }
             } else {
                 R pz = O::mul(dinv0[r], s0);
                 r0[r] = s0;
                 p0[r] = pz;
                 bb0 += s0 * s0;
                 rz0 += s0 * pz;
+                if (cm.world > 1 && r >= hp.n_int) {
+                    push_boundary_row<R>(hp, kVecP0, r, pz);
+                    pushed = true;
+                }
             }
         }
         __syncthreads();
@@ -523,9 +555,10 @@ __global__ void __launch_bounds__(kBlock) rhs_init(const int* __restrict__ rowpt
             part[3 * gridDim.x + blockIdx.x] = rz1;
         }
     }
-    if (cm.world > 1) {
+    if (publish) {  // totals -> every rank's mailbox (persistent solve kernels and partitioned handles start from there)
+        if (cm.world > 1 && __syncthreads_or(pushed ? 1 : 0)) __threadfence_system();
         __syncthreads();
-        ar_publish<R, (EQ == 3 ? 4 : 2)>(cm, part, (int)gridDim.x, red);
+        ar_publish<R, (EQ == 3 ? 4 : 2)>(cm, part, (int)gridDim.x, red, &hp, cm.world > 1);
     }
 }
 
@@ -534,26 +567,63 @@ __global__ void __launch_bounds__(kBlock) rhs_init(const int* __restrict__ rowpt
 // map_vector_to_surface incl. Dirichlet zeros (:28-36); has_numerical_instability (:41-48) as a sticky flag.
 // sol_is_v: Gray-Scott writes v back to the surface (:144); the other equations write u.
 // ------------------------------------------------------------------------------------------------
+// Partitioned handle: the owner of a boundary row also stores the row's u, v and surface value into the neighbours that
+// keep it as a ghost (they read them in the next step's RHS), and the last CTA raises the neighbours' state flags.
+// unstable: stamped with the step number (no reset launch per step); feab_unstable compares it with the current step.
 template <typename R>
-__global__ void finish_step(float* __restrict__ values, const int* __restrict__ idx_map, const int* __restrict__ rowmap, int64_t V,
-                            R* __restrict__ u, R* __restrict__ v, int wave, R dt, int sol_is_v, int* __restrict__ unstable) {
+__global__ void __launch_bounds__(kBlock) finish_step(float* __restrict__ values, const int* __restrict__ idx_map,
+                                                      const int* __restrict__ rowmap, int64_t V, R* __restrict__ u, R* __restrict__ v,
+                                                      int wave, R dt, int sol_is_v, int* __restrict__ unstable, int stamp, Comm cm,
+                                                      HaloPlan hp) {
+    if (cm.world > 1 && comm_failed(cm)) return;  // fail closed: a solve that lost a peer writes nothing back
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    bool bad = false;
+    bool bad = false, pushed = false;
     if (i < V) {
         int m = rowmap[i];  // == idx_map on one GPU; on a partition only the owned nodes are written
         if (m >= 0) {
             R ui = u[m], vi = v[m];
-            if (wave) {
-                ui = Ops<R>::add(ui, Ops<R>::mul(vi, dt));
+            if (wave) {  // u here is last step's result: it passed through surface->values (float) in between
+                ui = Ops<R>::add(through_float(ui), Ops<R>::mul(vi, dt));
                 u[m] = ui;
             }
-            values[i] = (float)(sol_is_v ? vi : ui);
+            const float out = (float)(sol_is_v ? vi : ui);
+            values[i] = out;
             bad = ui > (R)1e4f || vi > (R)1e4f;
+            if (cm.world > 1 && m >= hp.n_int) {
+                const int* t = hp.push_tab + (size_t)(m - hp.n_int) * hp.nnb;
+                for (int b = 0; b < hp.nnb; b++) {
+                    const int d = t[b];
+                    if (d >= 0) {
+                        const int q = hp.nb_rank[b];
+                        reinterpret_cast<R*>(hp.base[q] + hp.off_vec[kVecU][q])[d] = ui;
+                        reinterpret_cast<R*>(hp.base[q] + hp.off_vec[kVecV][q])[d] = vi;
+                        reinterpret_cast<float*>(hp.base[q] + hp.off_vec[kVecValues][q])[i] = out;
+                        pushed = true;
+                    }
+                }
+            }
         } else if (idx_map[i] < 0) {
             values[i] = 0.0f;
         }
     }
-    if (__any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0) atomicOr(unstable, 1);
+    if (__any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0) atomicMax(unstable, stamp);
+    if (cm.world > 1) {
+        __shared__ int s_last;
+        if (__syncthreads_or(pushed ? 1 : 0)) __threadfence_system();
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            __threadfence();
+            s_last = atomicAdd(&cm.loc->ticket, 1u) == gridDim.x - 1 ? 1 : 0;
+        }
+        __syncthreads();
+        if (s_last && threadIdx.x == 0) {
+            cm.loc->ticket = 0;
+            __threadfence_system();
+            const unsigned long long s = cm.loc->state_seq + 1;
+            cm.loc->state_seq = s;
+            for (int b = 0; b < hp.nnb; b++) st_release_sys(&cm.ctrl[hp.nb_rank[b]]->state_flag[cm.rank], s);
+        }
+    }
 }
 
 __global__ void brush_nodes(float* __restrict__ values, const long long* __restrict__ nodes, int64_t count, int64_t V, float strength) {

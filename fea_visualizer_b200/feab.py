@@ -246,7 +246,7 @@ class Feab:
     def pcg_profile(self, reset=True):
         out = (C.c_double * 16)()
         self._ck(self.lib.feab_pcg_profile(self.h, out, C.c_int(1 if reset else 0)))
-        names = ["spmv", "bar1", "ar1", "update", "bar2", "ar2", "direction", "bar3", "push"]
+        names = ["spmv", "sync1", "unused1", "update", "sync2", "unused2", "direction", "sync3", "unused3"]
         return {"ns": dict(zip(names, list(out)[:9])), "iterations": int(out[9])}
 
     def device_info(self):

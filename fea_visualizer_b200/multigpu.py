@@ -128,3 +128,43 @@ class VirtualRanks:
 
     def close(self):
         self._all("close")
+
+
+class ThreadedRanks(VirtualRanks):
+    """P partitioned handles on ONE device, each advanced by its own host thread through the ordinary feab_step: the
+    PRODUCTION multi-GPU kernels (persistent pcg_dual / pcg_persistent / bicg_persistent with their in-kernel grid syncs,
+    mailbox all-reduces, halo pushes and flags) run concurrently and talk through same-process peer pointers.  Their
+    cooperative grids must be co-resident, so every handle's grid is capped at SMs / P CTAs (FEAB_PCG_MAX_GRID: half of what one
+    handle alone may use, which keeps room for the short kernels of a rank that is one launch behind), and CUDA_DEVICE_MAX_CONNECTIONS must give
+    every stream its own hardware queue (tests/conftest.py sets 32).
+    This is what lets a ONE-GPU box check the kernels the N-GPU benchmark times."""
+
+    def __init__(self, world, real=64, device=0, part=None, sm_count=148, **solver):
+        import os
+        old = os.environ.get("FEAB_PCG_MAX_GRID")
+        os.environ["FEAB_PCG_MAX_GRID"] = str(max(1, sm_count // world))
+        try:
+            super().__init__(world, real=real, device=device, part=part, **solver)
+        finally:
+            if old is None:
+                del os.environ["FEAB_PCG_MAX_GRID"]
+            else:
+                os.environ["FEAB_PCG_MAX_GRID"] = old
+
+    def step(self, nsteps=1):
+        import threading
+        errs = []
+
+        def run(h):
+            try:
+                h.step(nsteps)
+            except Exception as e:  # noqa: BLE001 - re-raised below
+                errs.append(e)
+
+        ts = [threading.Thread(target=run, args=(h,)) for h in self.hs]
+        for t in ts:
+            t.start()
+        for t in ts:
+            t.join()
+        if errs:
+            raise errs[0]

@@ -189,9 +189,11 @@ int feab_mg_group_step(FeabHandle** handles, int count, int nsteps);
  * launch (CUDA events on the solver stream) and the algorithmic bytes one launch moves.
  * kernel: 0 = SpMV+dot, 1 = PCG vector update, 2 = PCG direction update, 3 = RHS build for the current equation */
 int feab_time_kernel(FeabHandle* h, int kernel, int reps, double* ms_per_launch, double* algorithmic_bytes);
-/* With FEAB_PCG_PROF=1 in the environment at feab_create: nanoseconds CTA 0 of the persistent PCG kernel spent in
- * [0] SpMV phase, [1] barrier + partial sums, [2] all-reduce of p.Ap, [3] update phase, [4] barrier + sums, [5] all-reduce
- * of |r|^2, r.z, [6] direction phase, [7] barrier, [8] halo push; [9] = iterations counted.  Zeros when profiling is off. */
+/* With FEAB_PCG_PROF=1 (pcg_persistent) or 2 (pcg_dual) in the environment at feab_create: nanoseconds CTA 0 of the
+ * persistent PCG kernel spent in [0] SpMV phase, [1] grid sync merged with the all-reduce of p.Ap, [3] update phase,
+ * [4] grid sync merged with the all-reduce of |r|^2, r.z, [6] direction phase (incl. halo stores), [7] grid sync that
+ * raises the halo flags; [2], [5], [8] unused (they were separate all-reduce / push stages before the syncs were merged);
+ * [9] = iterations counted.  Zeros when profiling is off. */
 int feab_pcg_profile(FeabHandle* h, double* out16, int reset);
 int feab_device_info(const FeabHandle* h, int* sm_count, int64_t* total_mem_bytes, char* name64);
 

@@ -1,6 +1,11 @@
 import os
 import sys
 
+# The threaded virtual-rank tests run up to 8 handles (16 streams) whose persistent kernels wait for each other on ONE
+# device: give every stream its own hardware queue, or kernels of different "ranks" that share a queue serialise and
+# deadlock (must be set before the CUDA context exists; irrelevant to the one-process-per-GPU production layout).
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)

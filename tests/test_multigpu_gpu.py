@@ -187,3 +187,71 @@ def test_one_process_per_gpu_partitioned_solve():
            "--master-port", str(port), os.path.join(root, "tests", "mp_partitioned.py")]
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=900, cwd=root)
     assert out.returncode == 0 and "MP_PARTITIONED_OK" in out.stdout, out.stdout[-3000:] + out.stderr[-3000:]
+
+
+# ---- the PRODUCTION multi-GPU kernels on one GPU: one host thread per virtual rank, ordinary feab_step ----------------
+def threaded(world, real, xyz, tri, ob, bc, part=None, **solver):
+    from fea_visualizer_b200.multigpu import ThreadedRanks
+    sm = feab.Feab(real=64).device_info()["sm_count"]
+    G = ThreadedRanks(world, real=real, part=part, sm_count=sm, **solver)
+    for h in G.hs:
+        h.set_boundary_condition(bc)
+    G.set_mesh(xyz, tri, ob)
+    return G
+
+
+@pytest.mark.parametrize("name,bc", [("ico12", 0), ("disk14", 0), ("disk14", 1)])
+@pytest.mark.parametrize("world", [2, 4, 8])
+@pytest.mark.parametrize("eq", [0, 1, 2, 3])
+def test_threaded_ranks_persistent_kernels_step_parity(name, bc, world, eq):
+    """Same bars as the lock-step test above, but through feab_step on every rank concurrently: pcg_dual / pcg_persistent
+    with world > 1 (grid syncs merged with the mailbox all-reduce, halo stores fused into the direction phase and the RHS
+    kernel, state pushes fused into the epilogue) -- the kernels bench.py times at N > 1."""
+    xyz, tri, ob = mesh(name)
+    V = len(xyz)
+    F = single(64, xyz, tri, ob, bc)
+    G = threaded(world, 64, xyz, tri, ob, bc)
+    D = O.Oracle(xyz, tri, ob, bc, real=64)
+    ref = []
+    run_steps(F, V, eq, 5, per_step=lambda s, X: ref.append((X.get_values(), X.get_state(0), X.get_state(1), X.stats()["iterations"])))
+    orc = []
+    run_steps(D, V, eq, 5, per_step=lambda s, X: orc.append((X.get_values(), X.get_state(0), X.get_state(1))))
+    worst = [0.0, 0.0]
+
+    def check(s, X):
+        v, u, vv, it = ref[s]
+        worst[0] = max(worst[0], rel_l2(X.get_values(), v), rel_l2(X.get_state(0), u), rel_l2(X.get_state(1), vv))
+        worst[1] = max(worst[1], rel_l2(X.get_values(), orc[s][0]), rel_l2(X.get_state(0), orc[s][1]), rel_l2(X.get_state(1), orc[s][2]))
+        git = X.stats()["iterations"]
+        assert abs(git[0] - it[0]) <= 2 and abs(git[1] - it[1]) <= 2, (git, it)
+        if eq == 3:
+            assert X.stats()["shared_iterations"] > 0     # the lock-step kernel ran on the partition
+
+    run_steps(G, V, eq, 5, per_step=check)
+    assert worst[0] <= 1e-11, worst      # vs single GPU: summation order only
+    assert worst[1] <= 1e-8, worst       # vs the fp64 oracle: the north star's per-step bar
+    assert G.unstable() == F.unstable()
+
+
+@pytest.mark.parametrize("world", [2, 8])
+def test_threaded_ranks_many_tiles_per_cta_and_device_resident_steps(world):
+    """~92 k rows: with the grid capped at 296 / world CTAs every CTA walks several tiles and the halo wait sits in the middle
+    of a tile loop; 6 steps in ONE call (no gather between steps: the RHS kernel re-reads the solver's own vector through
+    float) against the fp64 oracle stepping one by one."""
+    xyz, tri = meshes.icosphere(96)
+    ob = meshes.boundary_flags(len(xyz), tri)
+    V = len(xyz)
+    G = threaded(world, 64, xyz, tri, ob, 0)
+    D = O.Oracle(xyz, tri, ob, 0, real=64)
+    v0 = np.zeros(V, np.float32)
+    v0[meshes.seed_nodes(V)] = 1.0
+    for eq in (3, 1):
+        for X in (G, D):
+            X.clear()
+            X.set_equation(eq)
+            X.set_values(v0)
+        G.step(6)
+        for _ in range(6):
+            D.step(1)
+        assert rel_l2(G.get_values(), D.get_values()) <= 1e-6      # values are float32
+        assert rel_l2(G.get_state(0), D.get_state(0)) <= 1e-8 and rel_l2(G.get_state(1), D.get_state(1)) <= 1e-8

@@ -412,3 +412,27 @@ def test_c3_wave_1m_vertices_properties():
     F.step(3)
     assert np.isfinite(F.get_values()).all() and not F.unstable()
     assert F.stats()["rel_residual"][0] < 2.3e-16
+
+
+@pytest.mark.parametrize("eq", [0, 1, 2, 3])
+def test_device_resident_steps_equal_host_round_trips_bit_for_bit(eq):
+    """feab_step(NULL, n, 0) skips the values -> vector gather between steps (the RHS kernel re-reads the solver's own
+    result through float instead); n calls with a host round trip of surface->values in between gather every time.  Same
+    bits: surface->values is float in the reference, so the vector passes through float once per step either way
+    (CPUSolver.cpp:13-36)."""
+    xyz, tri = meshes.icosphere(10)
+    ob = meshes.boundary_flags(len(xyz), tri)
+    V = len(xyz)
+    v0 = np.zeros(V, np.float32)
+    v0[meshes.seed_nodes(V)] = 1.0
+    A = make(64, xyz, tri, ob, 0, assembly=feab.ASSEMBLY_ORDERED)
+    B = make(64, xyz, tri, ob, 0, assembly=feab.ASSEMBLY_ORDERED)
+    for X in (A, B):
+        X.set_equation(eq)
+        X.set_values(v0)
+    A.step(5)
+    for _ in range(5):
+        B.step(1)
+        B.set_values(B.get_values())
+    assert (A.get_values() == B.get_values()).all()
+    assert (A.get_state(0) == B.get_state(0)).all() and (A.get_state(1) == B.get_state(1)).all()
