@@ -1233,15 +1233,18 @@ class SolverT final : public SolverBase {
         read_states(st, &b);
         if (use_bicgstab()) {
             s->iterations[0] = b.iters;
+            s->spmv_passes[0] = 2 * (int64_t)b.trips;
             s->rel_residual[0] = b.rhs_norm > 0 ? (double)(b.r_norm / b.rhs_norm) : 0.0;
         } else {
             for (int i = 0; i < 2; i++) {
                 s->iterations[i] = st[i].iters;
+                s->spmv_passes[i] = st[i].iter1;
                 s->rel_residual[i] = st[i].rhs2 > 0 ? std::sqrt((double)st[i].rn2 / (double)st[i].rhs2) : 0.0;
             }
             if (eq_ != FEAB_EQ_REACTION_DIFFUSION) {
                 s->iterations[1] = 0;
                 s->rel_residual[1] = 0;
+                s->spmv_passes[1] = 0;
             }
         }
         s->last_call_ms = last_ms_;

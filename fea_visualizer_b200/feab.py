@@ -44,7 +44,7 @@ class FeabSolverOptions(C.Structure):
 class FeabStats(C.Structure):
     _fields_ = [("iterations", C.c_int64 * 2), ("rel_residual", C.c_double * 2), ("last_call_ms", C.c_double),
                 ("last_call_steps", C.c_int64), ("kernel_launches", C.c_int64), ("solve_ms", C.c_double),
-                ("shared_iterations", C.c_int64)]
+                ("shared_iterations", C.c_int64), ("spmv_passes", C.c_int64 * 2)]
 
 
 class FeabMgExport(C.Structure):
@@ -226,7 +226,7 @@ class Feab:
         self._ck(self.lib.feab_last_stats(self.h, C.byref(s)))
         return {"iterations": list(s.iterations), "rel_residual": list(s.rel_residual), "last_call_ms": s.last_call_ms,
                 "last_call_steps": s.last_call_steps, "kernel_launches": s.kernel_launches, "solve_ms": s.solve_ms,
-                "shared_iterations": s.shared_iterations}
+                "shared_iterations": s.shared_iterations, "spmv_passes": list(s.spmv_passes)}
 
     def get_state(self, which):
         out = np.empty(max(self.num_unknowns(), 1), dtype=self.real)

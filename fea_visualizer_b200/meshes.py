@@ -166,6 +166,22 @@ def disk(rings: int, radius: float = 1.0):
     return pos.astype(np.float32), np.asarray(tris, dtype=np.uint32)
 
 
+def fan_refined(xyz: np.ndarray, tri: np.ndarray):
+    """Every triangle (a, b, c) of a base mesh split at its centroid m into (a, b, m), (b, c, m), (c, a, m); the centroids
+    are appended AFTER the base vertices.  A base vertex of valence d gets valence 2 d, so on a regular base mesh the
+    first rows of the system have 13 entries each while the centroid rows have 4: consecutive 256 / 512-row tiles of the
+    base block hold more than 8 entries per row, which is what pushes the tile kernels (spmv_dot_tma, rhs_init_tma,
+    pcg_persistent, pcg_dual) onto their un-staged path (tile entries > the staging capacity)."""
+    xyz = np.asarray(xyz, dtype=np.float32)
+    t = np.asarray(tri, dtype=np.int64)
+    V = len(xyz)
+    cen = (xyz[t[:, 0]].astype(np.float64) + xyz[t[:, 1]] + xyz[t[:, 2]]) / 3.0
+    m = V + np.arange(len(t), dtype=np.int64)
+    out = np.concatenate([np.stack([t[:, 0], t[:, 1], m], 1), np.stack([t[:, 1], t[:, 2], m], 1), np.stack([t[:, 2], t[:, 0], m], 1)], axis=0)
+    return (np.ascontiguousarray(np.concatenate([xyz, cen.astype(np.float32)], 0), dtype=np.float32),
+            np.ascontiguousarray(out, dtype=np.uint32))
+
+
 def load_obj(path: str):
     """Minimal OBJ ingest following /root/reference/src/Utils/Surface.cpp:57-102: vertices in file
     order, faces as vertex-index triples, polygons fan-triangulated, a file without 'vn' lines is

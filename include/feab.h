@@ -87,6 +87,8 @@ typedef struct {
     double solve_ms;           /* PERSISTENT loop: device time of the PCG kernel(s) of the LAST step of the last call; else 0 */
     int64_t shared_iterations; /* Gray-Scott: SpMV passes of the last step in which the u- and the v-solve ran in lock-step
                                   from one index stream (pcg_dual.cuh); 0 when the two solves ran one after the other */
+    int64_t spmv_passes[2];    /* SpMV (+ update) passes each solve of the last step really ran: Eigen's iterations() is one less
+                                  for a solve that stopped on its residual test (ConjugateGradient.h:72-73 breaks before counting) */
 } FeabStats;
 
 /* -- lifetime ------------------------------------------------------------------------------- */

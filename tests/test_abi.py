@@ -50,7 +50,7 @@ def test_struct_fields_follow_the_header_order():
 def test_struct_layouts_match_header():
     assert C.sizeof(feab.FeabParams) == 20
     assert C.sizeof(feab.FeabSolverOptions) == 32
-    assert C.sizeof(feab.FeabStats) == 2 * 8 + 2 * 8 + 8 + 8 + 8 + 8 + 8
+    assert C.sizeof(feab.FeabStats) == 2 * 8 + 2 * 8 + 8 + 8 + 8 + 8 + 8 + 2 * 8
 
 
 def test_no_gpu_means_error_not_fallback(lib):

@@ -175,3 +175,56 @@ def test_c5_gray_scott_16m_vertices_properties():
     for _ in range(3):
         G.step(1)
     assert rel_l2(G.get_values(), F.get_values()) <= 1e-6      # scatter assembly: atomic order differs between handles
+
+
+# ------------------------------------------------------------------------------------------------- full size vs the oracle
+def test_c3_wave_1m_vertices_two_steps_against_the_oracle():
+    """configs[2] at its full size (icosphere nu = 316, 998 562 rows), wave equation, reference defaults: the field and the
+    hidden velocity after each of two steps against the fp64 oracle.  Bar: 1e-8 relative L2 per step (the north star's)."""
+    nu = 316
+    xyz, tri = meshes.icosphere(nu, radius=nu / 32.0)
+    V = len(xyz)
+    ob = np.zeros(V, np.uint8)
+    F = feab.Feab(real=64)
+    F.set_mesh(xyz, tri, ob)
+    D = O.Oracle(xyz, tri, ob, 0, real=64)
+    for X in (F, D):
+        X.clear()
+        X.set_equation(1)
+        X.set_values(_seeded(V))
+    for s in range(2):
+        F.step(1)
+        D.step(1)
+        e = [rel_l2(F.get_values(), D.get_values()), rel_l2(F.get_state(0), D.get_state(0)), rel_l2(F.get_state(1), D.get_state(1))]
+        assert max(e) <= 1e-8, (s, e)
+        assert abs(F.stats()["iterations"][0] - int(D.last_stats()[0][0])) <= 3
+
+
+@pytest.mark.timeout(1500)
+def test_c5_gray_scott_16m_vertices_one_step_against_the_oracle():
+    """configs[4], the benchmark mesh itself (icosphere nu = 1265, 16 002 252 rows): one seeded Gray-Scott step through the
+    production kernels (pcg_dual + pcg_persistent tail) against the fp64 oracle (about 80 s of CPU).  Bar: 1e-8 relative
+    L2 for u, v and surface->values; iteration counts within 3 of the oracle's."""
+    nu = 1265
+    xyz, tri = meshes.icosphere(nu, radius=nu / 32.0)
+    V = len(xyz)
+    ob = np.zeros(V, np.uint8)
+    F = feab.Feab(real=64)
+    F.set_mesh(xyz, tri, ob)
+    F.set_equation(3)
+    F.clear()
+    F.set_values(_seeded(V))
+    F.step(1)
+    st = F.stats()
+    got = [F.get_values(), F.get_state(0), F.get_state(1)]
+    assert st["shared_iterations"] > 0
+    F.close()
+    D = O.Oracle(xyz, tri, ob, 0, real=64)
+    D.clear()
+    D.set_equation(3)
+    D.set_values(_seeded(V))
+    D.step(1)
+    e = [rel_l2(got[0], D.get_values()), rel_l2(got[1], D.get_state(0)), rel_l2(got[2], D.get_state(1))]
+    assert max(e) <= 1e-8, e
+    oit = D.last_stats()[0]
+    assert abs(st["iterations"][0] - int(oit[0])) <= 3 and abs(st["iterations"][1] - int(oit[1])) <= 3, (st["iterations"], oit)

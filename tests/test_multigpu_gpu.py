@@ -255,3 +255,26 @@ def test_threaded_ranks_many_tiles_per_cta_and_device_resident_steps(world):
             D.step(1)
         assert rel_l2(G.get_values(), D.get_values()) <= 1e-6      # values are float32
         assert rel_l2(G.get_state(0), D.get_state(0)) <= 1e-8 and rel_l2(G.get_state(1), D.get_state(1)) <= 1e-8
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_threaded_ranks_rows_above_the_tile_staging_capacity(world):
+    """The un-staged tile path (rows with 13 entries in whole tiles, meshes.fan_refined) of the partitioned persistent kernels:
+    Gray-Scott through pcg_dual and heat through pcg_persistent on 2 / 4 concurrent virtual ranks vs the fp64 oracle."""
+    bx, bt = meshes.icosphere(28, radius=28 / 32.0)
+    xyz, tri = meshes.fan_refined(bx, bt)
+    V = len(xyz)
+    ob = meshes.boundary_flags(V, tri)
+    G = threaded(world, 64, xyz, tri, ob, 0)
+    assert all(h.counts()[3] >= 12 for h in G.hs)
+    D = O.Oracle(xyz, tri, ob, 0, real=64)
+    for eq in (3, 0):
+        orc = []
+        run_steps(D, V, eq, 4, per_step=lambda s, X: orc.append((X.get_values(), X.get_state(0), X.get_state(1))))
+        worst = [0.0]
+
+        def check(s, X):
+            worst[0] = max(worst[0], rel_l2(X.get_values(), orc[s][0]), rel_l2(X.get_state(0), orc[s][1]), rel_l2(X.get_state(1), orc[s][2]))
+
+        run_steps(G, V, eq, 4, per_step=check)
+        assert worst[0] <= 1e-8, (eq, worst)

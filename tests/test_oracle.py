@@ -203,3 +203,36 @@ def test_adv_diff_parity_mode_is_cg_on_transpose_and_bicgstab_is_correct():
     assert res(xb) < 1e-12
     assert res(xp) > 1e-4                      # reference behaviour: not a solution of the true system ...
     assert rel_l2(xp, xb) > 1e-4               # ... and visibly different from it
+
+
+def test_unit_sphere_gray_scott_blows_up_in_the_reference_itself():
+    """Why bench.py scales the icosphere to radius nu / 32 instead of SURVEY 8(d)'s unit sphere: on the
+    unit sphere at ~1e5 vertices the UNMODIFIED reference's Gray-Scott step (reaction terms not mass-weighted,
+    src/FEM/CPUSolver.cpp:134,137) leaves the seeded field growing without bound -- max|v| passes 1e3 after 5 steps and
+    has_numerical_instability() (src/FEM/CPUSolver.cpp:41-48) fires on the 6th -- while the same mesh at the bundled
+    icosphere.obj's element size stays bounded.  A unit-sphere benchmark would time Eigen's 2n-iteration NaN loop."""
+    if not O.reference_available():
+        pytest.skip("oracle/_ref not built (needs /root/reference)")
+    for radius, blows in ((1.0, True), (100 / 32.0, False)):
+        xyz, tri = meshes.icosphere(100, radius=radius)
+        V = len(xyz)
+        R = O.Reference(xyz, tri, np.zeros(V, np.uint8), 0)
+        R.set_equation(3)
+        seeds = meshes.seed_nodes(V)
+        fired = None
+        peak = 0.0
+        for s in range(6):
+            if s < 5:
+                v = R.get_values()
+                v[seeds] = 1.0
+                R.set_values(v)
+            R.step(1)
+            peak = max(peak, float(np.nanmax(np.abs(R.get_values()))))
+            if R.unstable():
+                fired = s
+                break
+        if blows:
+            assert fired is not None and fired <= 5 and peak > 1e3, (fired, peak)
+        else:
+            assert fired is None and peak <= 1.0, (fired, peak)
+        R.close()

@@ -436,3 +436,43 @@ def test_device_resident_steps_equal_host_round_trips_bit_for_bit(eq):
         B.set_values(B.get_values())
     assert (A.get_values() == B.get_values()).all()
     assert (A.get_state(0) == B.get_state(0)).all() and (A.get_state(1) == B.get_state(1)).all()
+
+
+# ---------------------------------------------------------------------------------------------- tiles above the staging capacity
+def _fan_cases():
+    bx, bt = meshes.icosphere(20, radius=20 / 32.0)
+    gx, gt = meshes.grid(40, 30, 1.25, 0.9375)
+    return {"fan_ico20": meshes.fan_refined(bx, bt), "fan_grid40x30": meshes.fan_refined(gx, gt)}
+
+
+@pytest.mark.parametrize("name,bc", [("fan_ico20", 0), ("fan_grid40x30", 0), ("fan_grid40x30", 1)])
+@pytest.mark.parametrize("eq", [0, 1, 2, 3])
+@pytest.mark.parametrize("loop", [feab.LOOP_PERSISTENT, feab.LOOP_GRAPH_WHILE])
+def test_rows_above_the_tile_staging_capacity(name, bc, eq, loop):
+    """Fan-refined meshes (meshes.fan_refined): the base vertices come first and have 13 entries per row, so whole 256- and
+    512-row tiles hold more than 8 entries per row and the tile kernels take their un-staged path (spmv_dot_tma, rhs_init_tma,
+    pcg_persistent, pcg_dual read values / columns straight from global memory); the tile that straddles the base block and the
+    centroid rows is staged with rows longer than 8 (the `len >= 8` tail).  All four equations, Gray-Scott through pcg_dual
+    (persistent driver) and through the three-kernel WHILE graph.  Bar: 1e-8 relative L2 per step vs the fp64 oracle."""
+    xyz, tri = _fan_cases()[name]
+    V = len(xyz)
+    ob = meshes.boundary_flags(V, tri)
+    D = O.Oracle(xyz, tri, ob, bc, real=64)
+    F = make(64, xyz, tri, ob, bc, assembly=feab.ASSEMBLY_ORDERED, loop_mode=loop)
+    _, n, nnz, max_row = F.counts()
+    rowptr, _, _ = F.csr(0)
+    assert max_row >= 13 and int(rowptr[512]) > 8 * 512 and int(rowptr[256]) > 8 * 256      # first tiles exceed TmaCfg::kCap / DualCfg cap
+    ref = []
+    run_steps(D, V, eq, 5, per_step=lambda s, X: ref.append((X.get_values(), X.get_state(0), X.get_state(1), X.last_stats()[0].copy())))
+    worst = [0.0]
+
+    def check(s, X):
+        v, u, vv, it = ref[s]
+        worst[0] = max(worst[0], rel_l2(X.get_state(0), u), rel_l2(X.get_state(1), vv), rel_l2(X.get_values(), v))
+        git = X.stats()["iterations"]
+        assert abs(git[0] - it[0]) <= 3 and abs(git[1] - it[1]) <= 3, (git, it)
+
+    run_steps(F, V, eq, 5, per_step=check)
+    assert worst[0] <= FP64_STEP_TOL, worst[0]
+    if eq == 3 and loop == feab.LOOP_PERSISTENT:
+        assert F.stats()["shared_iterations"] > 0          # the lock-step kernel ran these tiles
