@@ -455,6 +455,7 @@ def main():
     launches = st["kernel_launches"] - launches0
     solve_ms = st.get("solve_ms", 0.0)       # persistent loop: device time of the last step's PCG kernel(s)
     prof = F.pcg_profile(reset=True)          # FEAB_PCG_PROF=1: where CTA 0 of the persistent kernel spent its time
+    step_ms = {"value_leg_last_step": prof["step_ms"]} if any(prof["step_ms"].values()) else None   # FEAB_STEP_PROF=1
     if prof["iterations"]:
         prof = {"us_per_iteration": {k: v / prof["iterations"] / 1e3 for k, v in prof["ns"].items()}, "iterations": prof["iterations"]}
         sys.stderr.write(f"[rank {rank}] pcg phase profile: {json.dumps(prof)}\n")
@@ -474,6 +475,9 @@ def main():
     e2e_s = time.perf_counter() - t0
     barrier()
     its_e2e = F.stats()["iterations"]
+    if step_ms is not None:
+        step_ms["e2e_leg_last_step"] = F.pcg_profile(reset=False)["step_ms"]
+        sys.stderr.write(f"[rank {rank}] step phases (ms): {json.dumps(step_ms)}\n")
     clocks = sampler.stop() if rank == 0 else None
 
     t = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
@@ -569,7 +573,7 @@ def main():
                 "e2e": {"value": e2e_value, "unit": "steps/s", "h2d_bytes_per_step": 4 * V, "d2h_bytes_per_step": 4 * V,
                         "mode": "host buffers on rank 0 (FEAB_SYNC_ROOT), peers fed over NVLink" if world > 1 else "host buffers, full sync",
                         "pcg_iterations_last_step": its_e2e, "same_steps_as_value": list(its_e2e) == list(its), "le_value": e2e_value <= value},
-                "gpu_launches": launches_all, "pcg_phase_profile": prof, "parity": parity, "roofline": roof, "cpu_baseline": cpu, "clocks": clocks}
+                "gpu_launches": launches_all, "pcg_phase_profile": prof, "step_phase_ms": step_ms, "parity": parity, "roofline": roof, "cpu_baseline": cpu, "clocks": clocks}
         emit(line)
         if parity is not None and not parity["ok"]:
             sys.stderr.write(f"PARITY FAILED: {json.dumps(parity)}\n")

@@ -438,13 +438,20 @@ __global__ void __launch_bounds__(1024) state_push(Comm cm, HaloPlan hp, const R
 
 // surface->values is complete on every rank after advance_time() (the reference's data contract): each rank
 // broadcasts the values of the nodes it owns to all peers.  Grid-wide; the last CTA raises the flags.
+// root_only (FEAB_SYNC_ROOT): only rank 0's host array is read afterwards, so the owners store into rank 0's mirror only.
 __global__ void __launch_bounds__(kBlock) values_broadcast(Comm cm, HaloPlan hp, const int* __restrict__ row_node, int64_t n_own,
-                                                           const float* __restrict__ values) {
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_own; i += (int64_t)gridDim.x * blockDim.x) {
-        const int node = row_node[i];
-        const float val = values[node];
-        for (int q = 0; q < cm.world; q++)
-            if (q != cm.rank) reinterpret_cast<float*>(hp.base[q] + hp.off_vec[kVecValues][q])[node] = val;
+                                                           const float* __restrict__ values, int root_only) {
+    if (!(root_only && cm.rank == 0)) {
+        for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_own; i += (int64_t)gridDim.x * blockDim.x) {
+            const int node = row_node[i];
+            const float val = values[node];
+            if (root_only) {
+                reinterpret_cast<float*>(hp.base[0] + hp.off_vec[kVecValues][0])[node] = val;
+            } else {
+                for (int q = 0; q < cm.world; q++)
+                    if (q != cm.rank) reinterpret_cast<float*>(hp.base[q] + hp.off_vec[kVecValues][q])[node] = val;
+            }
+        }
     }
     __threadfence_system();
     __shared__ int s_last;
@@ -460,34 +467,16 @@ __global__ void __launch_bounds__(kBlock) values_broadcast(Comm cm, HaloPlan hp,
         const unsigned long long s = cm.loc->full_seq + 1;
         cm.loc->full_seq = s;
         for (int q = 0; q < cm.world; q++)
-            if (q != cm.rank) st_release_sys(&cm.ctrl[q]->full_flag[cm.rank], s);
+            if (q != cm.rank && (!root_only || q == 0)) st_release_sys(&cm.ctrl[q]->full_flag[cm.rank], s);
     }
 }
 
-// FEAB_SYNC_ROOT (feab.h): surface->values lives on the host of rank 0 only (the viewer process).  Rank 0 uploads it and
-// pushes the whole array into every peer's mirror over NVLink; the peers wait for the flag instead of touching PCIe.
-// Grid-wide, coalesced float4 stores; the last CTA raises the flags.
-__global__ void __launch_bounds__(kBlock) root_push(Comm cm, HaloPlan hp, int64_t V, const float* __restrict__ values) {
-    const int64_t nv4 = V / 4;
-    const float4* src = reinterpret_cast<const float4*>(values);
-    for (int q = 0; q < cm.world; q++) {
-        if (q == cm.rank) continue;
-        float* dstf = reinterpret_cast<float*>(hp.base[q] + hp.off_vec[kVecValues][q]);
-        float4* dst = reinterpret_cast<float4*>(dstf);
-        for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nv4; i += (int64_t)gridDim.x * blockDim.x) dst[i] = src[i];
-        if (blockIdx.x == 0)
-            for (int64_t i = nv4 * 4 + threadIdx.x; i < V; i += blockDim.x) dstf[i] = values[i];
-    }
-    __threadfence_system();
-    __shared__ int s_last;
-    __syncthreads();
+// FEAB_SYNC_ROOT (feab.h): surface->values lives on the host of rank 0 only (the viewer process).  Rank 0 uploads it into its
+// own mirror and raises every peer's root flag (this kernel, stream-ordered after the H2D copy); each peer waits for the flag
+// and then PULLS the values of its own columns (owned rows + ghosts) from rank 0's mirror over NVLink, inside its gather
+// kernel (solver.cuh gather_cols) -- V floats leave rank 0 in total, not V floats per peer.
+__global__ void root_signal(Comm cm) {
     if (threadIdx.x == 0) {
-        unsigned t = atomicAdd(&cm.loc->ticket, 1u);
-        s_last = (t == gridDim.x - 1) ? 1 : 0;
-    }
-    __syncthreads();
-    if (s_last && threadIdx.x == 0) {
-        cm.loc->ticket = 0;
         __threadfence_system();
         const unsigned long long s = cm.loc->root_seq + 1;
         cm.loc->root_seq = s;

@@ -15,6 +15,7 @@
 #include <vector>
 
 #include "assembly.cuh"
+#include "bicg_persistent.cuh"
 #include "bicgstab.cuh"
 #include "common.cuh"
 #include "partition.cuh"
@@ -183,6 +184,10 @@ class SolverT final : public SolverBase {
         pcg_max_grid_ = coop ? occ * sms_ : 0;
         if (const char* v = getenv("FEAB_PCG_CTAS_PER_SM")) pcg_max_grid_ = std::min(pcg_max_grid_, std::max(1, atoi(v)) * sms_);
         for (int i = 0; i < 4; i++) CK(cudaEventCreate(&ev_solve_[i]));
+        if (const char* v = getenv("FEAB_STEP_PROF")) {
+            step_prof_ = atoi(v) != 0;
+            for (int i = 0; i < 8; i++) CK(cudaEventCreate(&ev_ph_[i]));
+        }
         if (const char* v = getenv("FEAB_PCG_PROF")) {  // 1: stamps of pcg_persistent, 2: stamps of pcg_dual
             prof_dual_ = atoi(v) == 2;
             CK(cudaMalloc(&d_prof_, 16 * sizeof(unsigned long long)));
@@ -200,16 +205,70 @@ class SolverT final : public SolverBase {
         dual_max_grid_ = coop ? docc * sms_ : 0;
         if (dual_max_grid_ > 0) d_dpart_.alloc((size_t)6 * dual_max_grid_);
         if (const char* v = getenv("FEAB_DUAL")) dual_ = atoi(v) != 0;
+        if (const char* v = getenv("FEAB_ZIGZAG")) zigzag_ = atoi(v) != 0 ? 1 : 0;
+        // non-symmetric mode: the whole BiCGSTAB solve as one cooperative kernel (bicg_persistent.cuh), same tile geometry
+        CK(cudaFuncSetAttribute(bicg_persistent<R, kPcgRows, kPcgCpr, kPcgStages, kPcgMinB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)PCfg::kSmemBytes));
+        int bocc = 0;
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bocc, bicg_persistent<R, kPcgRows, kPcgCpr, kPcgStages, kPcgMinB>, kPcgRows,
+                                                         PCfg::kSmemBytes));
+        bicg_max_grid_ = coop ? bocc * sms_ : 0;
+        // CUDA loads kernels lazily, on their first launch, and that load may wait for the device to drain.  A partitioned
+        // step launches kernels while kernels of other ranks SPIN on flags this rank has yet to raise; if the launch that
+        // raises them is a first launch, the load and the spin wait for each other (seen with several ranks in one process).
+        // Touch every kernel of the stepping path once, here, while nothing is running.
+        preload_kernels();
         // several handles whose persistent kernels must be co-resident on ONE device (the threaded virtual-rank tests)
         if (const char* v = getenv("FEAB_PCG_MAX_GRID")) {
             const int g = std::max(1, atoi(v));
             pcg_max_grid_ = std::min(pcg_max_grid_, g);
             dual_max_grid_ = std::min(dual_max_grid_, g);
+            bicg_max_grid_ = std::min(bicg_max_grid_, g);
             grid_cap_ = g;  // also for the RHS kernel, whose CTAs wait for the neighbours' state flags
         }
     }
     static constexpr int kPcgRows = 512, kPcgCpr = 8, kPcgStages = 2, kPcgMinB = 2;
     static constexpr int kDualRows = 256;
+
+    template <typename F>
+    static void touch(F* f) {
+        cudaFuncAttributes at;
+        cudaFuncGetAttributes(&at, (const void*)f);
+        cudaGetLastError();
+    }
+    void preload_kernels() {
+        touch(wait_kernel);
+        touch(root_signal);
+        touch(root_wait);
+        touch(values_broadcast);
+        touch(pull_cols);
+        touch(brush_nodes);
+        touch(gather_values<R>);
+        touch(gather_cols<R>);
+        touch(finish_step<R>);
+        touch(finish_rows<R>);
+        touch(state_push<R>);
+        touch(halo_push<R>);
+        touch(build_operator<R>);
+        touch(inv_diag<R>);
+        touch(rhs_init<R, 0>);
+        touch(rhs_init<R, 1>);
+        touch(rhs_init<R, 2>);
+        touch(rhs_init<R, 3>);
+        touch(rhs_init_tma<R, 0, kRhsRows, kRhsCpr, kRhsStages, kRhsMinB>);
+        touch(rhs_init_tma<R, 2, kRhsRows, kRhsCpr, kRhsStages, kRhsMinB>);
+        touch(rhs_init_tma<R, 3, kRhsRows, kRhsCpr, kRhsStages, kRhsMinB>);
+        touch(ar_collect<R, 2>);
+        touch(ar_collect<R, 4>);
+        touch(cg_begin<R>);
+        touch(cg_update<R>);
+        touch(cg_direction<R>);
+        touch(spmv_dot<R>);
+        touch(spmv_dot_tma<R, 512, 8, 2, 2>);
+        touch(pcg_persistent<R, kPcgRows, kPcgCpr, kPcgStages, kPcgMinB>);
+        touch(pcg_dual<R, kDualRows, kPcgCpr, kPcgStages, kPcgMinB>);
+        touch(bicg_persistent<R, kPcgRows, kPcgCpr, kPcgStages, kPcgMinB>);
+    }
 
     // ---- SpMV variants: 0 = LDG/CSR-stream (solver.cuh), 1.. = TMA pipelines (spmv_tma.cuh) ----
     template <int ROWS, int CPR, int STAGES, int MINB>
@@ -272,6 +331,8 @@ class SolverT final : public SolverBase {
         if (d_prof_) cudaFree(d_prof_);
         for (int i = 0; i < 4; i++)
             if (ev_solve_[i]) cudaEventDestroy(ev_solve_[i]);
+        for (int i = 0; i < 8; i++)
+            if (ev_ph_[i]) cudaEventDestroy(ev_ph_[i]);
         close_peers();
         if (h_flag_) cudaFreeHost(h_flag_);
         cudaEventDestroy(ev0_);
@@ -462,6 +523,12 @@ class SolverT final : public SolverBase {
         d_node_of_.alloc(std::max<int64_t>(nglob_, 1));
         make_idx_map<<<gV, kBlock, 0, stream_>>>(flag.p, excl.p, V, d_idx_.p, d_node_of_.p);
         launches_ += 2;
+        n_dir_ = V - nglob_;
+        if (world_ > 1) {  // the partitioned epilogue walks rows, not nodes: it needs the Dirichlet nodes as a list
+            d_dir_nodes_.alloc(std::max<int64_t>(n_dir_, 1));
+            make_dirichlet_list<<<gV, kBlock, 0, stream_>>>(flag.p, excl.p, V, d_dir_nodes_.p);
+            launches_++;
+        }
         if (world_ > 1) {
             number_partition();
         } else {
@@ -760,7 +827,7 @@ class SolverT final : public SolverBase {
     }
     bool use_bicgstab() const { return eq_ == FEAB_EQ_ADVECTION_DIFFUSION && opt_.solver == FEAB_SOLVER_BICGSTAB; }
     // BiCGSTAB through the multi-kernel WHILE graph / host-batched loop (bicgstab.cuh) instead of the persistent kernel
-    bool use_bicgstab_legacy() const { return use_bicgstab(); }
+    bool use_bicgstab_legacy() const { return use_bicgstab() && (opt_.loop_mode != FEAB_LOOP_PERSISTENT || bicg_max_grid_ <= 0); }
 
     void ensure_operator() { ensure_operator_on(stream_); }
     void ensure_operator_on(cudaStream_t s) {
@@ -858,7 +925,11 @@ class SolverT final : public SolverBase {
         if (gather) {
             R* target = eq_ == FEAB_EQ_REACTION_DIFFUSION ? d_v_.p : d_u_.p;
             if (world_ > 1) wait_kernel<<<1, 32, 0, s>>>(cm_, hp_, 1);  // ghost values: the neighbours' end-of-step pushes have landed
-            gather_values<R><<<gV, kBlock, 0, s>>>(d_values_.p, colmap_p_, V_, target, cm_, hp_);
+            if (world_ > 1)
+                gather_cols<R><<<std::max(1, std::min({cdiv64(n_cols_, kBlock), sms_ * 4, grid_cap_})), kBlock, 0, s>>>(d_values_.p, node_of_col_p_, n_cols_,
+                                                                                                                    target, cm_);
+            else
+                gather_values<R><<<gV, kBlock, 0, s>>>(d_values_.p, colmap_p_, V_, target, cm_, hp_);
         }
         const int publish = (world_ > 1 || persistent_solves(capturing)) ? 1 : 0;
         launch_rhs(s, sc, part_rhs(), cm_, publish);
@@ -910,8 +981,13 @@ class SolverT final : public SolverBase {
         // a captured graph replays one stamp: it keeps the sticky semantics of a flag that is reset by feab_clear only
         const int stamp = capturing ? 1 : (step_stamp_ = step_stamp_ >= INT32_MAX - 1 ? 1 : step_stamp_ + 1);
         if (!capturing) last_stamp_ = stamp;
-        finish_step<R><<<gV, kBlock, 0, s>>>(d_values_.p, d_idx_.p, rowmap_p_, V_, d_u_.p, d_v_.p, eq_ == FEAB_EQ_WAVE ? 1 : 0, (R)scalars().dt,
-                                             eq_ == FEAB_EQ_REACTION_DIFFUSION ? 1 : 0, d_unstable_, stamp, cm_, hp_);
+        if (world_ > 1)
+            finish_rows<R><<<std::max(1, std::min({cdiv64(n_, kBlock), sms_ * 4, grid_cap_})), kBlock, 0, s>>>(
+                d_values_.p, node_of_col_p_, n_, d_dir_nodes_.p, n_dir_, d_u_.p, d_v_.p, eq_ == FEAB_EQ_WAVE ? 1 : 0, (R)scalars().dt,
+                eq_ == FEAB_EQ_REACTION_DIFFUSION ? 1 : 0, d_unstable_, stamp, cm_, hp_);
+        else
+            finish_step<R><<<gV, kBlock, 0, s>>>(d_values_.p, d_idx_.p, rowmap_p_, V_, d_u_.p, d_v_.p, eq_ == FEAB_EQ_WAVE ? 1 : 0, (R)scalars().dt,
+                                                 eq_ == FEAB_EQ_REACTION_DIFFUSION ? 1 : 0, d_unstable_, stamp, cm_, hp_);
         if (!capturing) launches_ += 1;
         CK(cudaGetLastError());
     }
@@ -960,6 +1036,7 @@ class SolverT final : public SolverBase {
         da.first_halo_tile = first_halo_tile(kDualRows);
         da.tol = tol();
         da.maxit = maxit();
+        da.zigzag = zigzag_;
         da.prof = prof_dual_ ? d_prof_ : nullptr;
         const int grid = std::min(dual_max_grid_, da.num_tiles);
         using DCfg = DualCfg<R, kDualRows, kPcgCpr, kPcgStages>;
@@ -995,12 +1072,50 @@ class SolverT final : public SolverBase {
         pa.begin = begin;
         pa.tol = tol();
         pa.maxit = maxit();
+        pa.zigzag = zigzag_;
         pa.prof = prof_dual_ ? nullptr : d_prof_;
         const int grid = std::min(pcg_max_grid_, pa.num_tiles);
         using PCfg = TmaCfg<R, kPcgRows, kPcgCpr, kPcgStages>;
         void* kargs[] = {(void*)&pa, (void*)&cm_, (void*)&hp_};
         CK(cudaLaunchCooperativeKernel((const void*)pcg_persistent<R, kPcgRows, kPcgCpr, kPcgStages, kPcgMinB>, dim3(grid), dim3(kPcgRows), kargs,
                                        PCfg::kSmemBytes, stream_));
+        launches_ += 1;
+    }
+
+    // Non-symmetric mode, persistent loop driver: the whole BiCGSTAB solve is one cooperative launch (bicg_persistent.cuh).
+    // Vectors: r = d_r_[0] (holds b from the RHS kernel), y = d_p_[0] and z = d_p_[1] (the arena vectors with ghost tails: the
+    // two vectors the SpMV gathers from), x = d_u_, p = d_w_[2], v = d_w_[1], r0 = d_w_[0], s = d_r_[1], t = d_y_, b = d_w_[4].
+    void launch_bicg_persistent() {
+        BicgArgs<R> ba;
+        ba.rowptr = d_rowptr_.p;
+        ba.col = d_col_.p;
+        ba.A = d_A0_.p;
+        ba.dinv = d_dinv0_.p;
+        ba.x = d_u_.p;
+        ba.r = d_r_[0].p;
+        ba.r0 = d_w_[0].p;
+        ba.v = d_w_[1].p;
+        ba.p = d_w_[2].p;
+        ba.y = d_p_[0].p;
+        ba.s = d_r_[1].p;
+        ba.z = d_p_[1].p;
+        ba.t = d_y_.p;
+        ba.b = d_w_[4].p;
+        ba.n = n_;
+        ba.num_tiles = std::max(1, cdiv64(n_, kPcgRows));
+        ba.first_halo_tile = first_halo_tile(kPcgRows);
+        ba.st = d_bst_;
+        ba.part = d_ppart_.p;
+        ba.tol = tol();
+        ba.maxit = maxit();
+        ba.prof = d_prof_;
+        const int grid = std::min(bicg_max_grid_, ba.num_tiles);
+        using PCfg = TmaCfg<R, kPcgRows, kPcgCpr, kPcgStages>;
+        void* kargs[] = {(void*)&ba, (void*)&cm_, (void*)&hp_};
+        if (time_solves_) CK(cudaEventRecord(ev_solve_[0], stream_));
+        CK(cudaLaunchCooperativeKernel((const void*)bicg_persistent<R, kPcgRows, kPcgCpr, kPcgStages, kPcgMinB>, dim3(grid), dim3(kPcgRows), kargs,
+                                       PCfg::kSmemBytes, stream_));
+        if (time_solves_) CK(cudaEventRecord(ev_solve_[1], stream_));
         launches_ += 1;
     }
 
@@ -1060,10 +1175,15 @@ class SolverT final : public SolverBase {
     void enqueue_bicgstab(const R* A, const R* dinv, R* x, bool capturing);  // bicgstab driver below
 
     void enqueue_step(bool capturing) {
+        if (!capturing) mark(1);
         ph_step_begin(stream_, capturing);
         ph_step_collect(stream_, capturing);
+        if (!capturing) mark(2);
         if (use_bicgstab()) {
-            enqueue_bicgstab(d_A0_.p, d_dinv0_.p, d_u_.p, capturing);
+            if (persistent_solves(capturing))
+                launch_bicg_persistent();
+            else
+                enqueue_bicgstab(d_A0_.p, d_dinv0_.p, d_u_.p, capturing);
         } else {
             const R* A[2];
             const R* dinv[2];
@@ -1075,7 +1195,9 @@ class SolverT final : public SolverBase {
             else
                 for (int slot = 0; slot < ns; slot++) enqueue_pcg(slot, A, dinv, x, capturing, ns);
         }
+        if (!capturing) mark(3);
         ph_finish(stream_, capturing);
+        if (!capturing) mark(4);
     }
 
     void drop_graphs() {
@@ -1106,7 +1228,9 @@ class SolverT final : public SolverBase {
         REQUIRE(have_mesh_, FEAB_ENOMESH, "step: no mesh");
         if (world_ > 1) {
             for (int q = 0; q < world_; q++) REQUIRE(connected_[q], FEAB_EINVAL, "step: partitioned handle is not connected to every peer (feab_mg_connect)");
-            REQUIRE(!use_bicgstab(), FEAB_EINVAL, "step: BiCGSTAB is not available on a partitioned mesh (use FEAB_SOLVER_PARITY_CG)");
+            REQUIRE(!use_bicgstab_legacy(), FEAB_EINVAL,
+                    "step: on a partitioned mesh BiCGSTAB needs the persistent loop driver (FEAB_LOOP_PERSISTENT); the WHILE-graph / host-batched "
+                    "BiCGSTAB kernels have no halo exchange");
             REQUIRE(n_ > 0, FEAB_EINVAL, "step: this rank owns no unknowns");
         }
     }
@@ -1130,12 +1254,16 @@ class SolverT final : public SolverBase {
         }
     }
     // surface->values complete on every rank: owners broadcast, everybody waits for everybody
-    void ph_broadcast_values(cudaStream_t s) {
+    // root_only (FEAB_SYNC_ROOT): the owners store into rank 0's mirror only and only rank 0 waits
+    void ph_broadcast_values(cudaStream_t s, bool root_only) {
         if (world_ == 1) return;
         const int g = std::max(1, std::min(cdiv64(n_, kBlock), sms_ * 4));
-        values_broadcast<<<g, kBlock, 0, s>>>(cm_, hp_, node_of_col_p_, n_, d_values_.p);
-        wait_kernel<<<1, 32, 0, s>>>(cm_, hp_, 2);
-        launches_ += 2;
+        values_broadcast<<<g, kBlock, 0, s>>>(cm_, hp_, node_of_col_p_, n_, d_values_.p, root_only ? 1 : 0);
+        launches_ += 1;
+        if (!root_only || rank_ == 0) {
+            wait_kernel<<<1, 32, 0, s>>>(cm_, hp_, 2);
+            launches_ += 1;
+        }
     }
 
     void step(float* values, int nsteps, int sync) override {
@@ -1149,12 +1277,19 @@ class SolverT final : public SolverBase {
         // that call, i.e. after the peers' last read of their mirrors.
         const bool root_mode = world_ > 1 && sync == FEAB_SYNC_ROOT && values != nullptr;
         if (values) values_dirty_ = true;
+        mark_now_ = true;
+        mark(0);
+        mark_now_ = false;
         if (root_mode) {
             if (rank_ == 0) {
                 CK(cudaMemcpyAsync(d_values_.p, values, V_ * sizeof(float), cudaMemcpyHostToDevice, stream_));
-                root_push<<<std::max(1, std::min(cdiv64(V_ / 4, kBlock), sms_ * 4)), kBlock, 0, stream_>>>(cm_, hp_, V_, d_values_.p);
+                root_signal<<<1, 32, 0, stream_>>>(cm_);
             } else {
+                // the values of this rank's columns (own rows + ghosts) come from rank 0's mirror over NVLink
                 root_wait<<<1, 32, 0, stream_>>>(cm_);
+                pull_cols<<<std::max(1, std::min({cdiv64(n_cols_, kBlock), sms_ * 4, grid_cap_})), kBlock, 0, stream_>>>(
+                    reinterpret_cast<const float*>(hp_.base[0] + hp_.off_vec[kVecValues][0]), node_of_col_p_, n_cols_, d_values_.p, cm_);
+                launches_++;
             }
             launches_++;
         } else if (values) {
@@ -1163,8 +1298,8 @@ class SolverT final : public SolverBase {
         if (n_ > 0 && nsteps > 0) {
             ensure_operator();
             ph_push_state(stream_);
-            // BiCGSTAB has no persistent kernel: it keeps the WHILE graph unless host batching was asked for
-            const bool graph_mode = opt_.loop_mode == FEAB_LOOP_GRAPH_WHILE || (opt_.loop_mode == FEAB_LOOP_PERSISTENT && use_bicgstab());
+            // a device without cooperative launch runs BiCGSTAB through the WHILE graph
+            const bool graph_mode = opt_.loop_mode == FEAB_LOOP_GRAPH_WHILE || (opt_.loop_mode == FEAB_LOOP_PERSISTENT && use_bicgstab_legacy());
             graph_mode_last_ = graph_mode;
             if (graph_mode) {
                 dual_last_ = false;  // a graph replays separate solves
@@ -1173,6 +1308,7 @@ class SolverT final : public SolverBase {
             if (graph_mode && (!graph_exec_ || graph_eq_ != eq_)) build_graph();
             for (int s = 0; s < nsteps; s++) {
                 time_solves_ = !graph_mode && opt_.loop_mode == FEAB_LOOP_PERSISTENT && s == nsteps - 1;
+                mark_now_ = !graph_mode && s == nsteps - 1;
                 if (graph_mode) {
                     CK(cudaGraphLaunch(graph_exec_, stream_));
                     graph_steps_++;
@@ -1181,12 +1317,29 @@ class SolverT final : public SolverBase {
                 }
             }
         }
-        if (values && sync) {
-            ph_broadcast_values(stream_);
-            if (!root_mode || rank_ == 0) CK(cudaMemcpyAsync(values, d_values_.p, V_ * sizeof(float), cudaMemcpyDeviceToHost, stream_));
+        const bool stepped = mark_now_;
+        mark_now_ = true;
+        if (!stepped) {
+            for (int i = 1; i <= 4; i++) mark(i);
         }
+        if (values && sync) {
+            ph_broadcast_values(stream_, root_mode);
+            mark(5);
+            if (!root_mode || rank_ == 0) CK(cudaMemcpyAsync(values, d_values_.p, V_ * sizeof(float), cudaMemcpyDeviceToHost, stream_));
+        } else {
+            mark(5);
+        }
+        mark(6);
+        mark_now_ = false;
         CK(cudaEventRecord(ev1_, stream_));
         CK(cudaStreamSynchronize(stream_));
+        if (step_prof_) {
+            for (int i = 0; i < 6; i++) {
+                float t = 0;
+                phase_ms_[i] = cudaEventElapsedTime(&t, ev_ph_[i], ev_ph_[i + 1]) == cudaSuccess ? t : 0.0;
+            }
+            cudaGetLastError();
+        }
         float ms = 0;
         CK(cudaEventElapsedTime(&ms, ev0_, ev1_));
         last_ms_ = ms;
@@ -1330,6 +1483,8 @@ class SolverT final : public SolverBase {
 
     void pcg_profile(double* out16, int reset) override {
         for (int i = 0; i < 16; i++) out16[i] = 0;
+        if (step_prof_)
+            for (int i = 0; i < 6; i++) out16[10 + i] = phase_ms_[i];
         if (!d_prof_) return;
         CK(cudaSetDevice(device_));
         unsigned long long h[16];
@@ -1509,7 +1664,8 @@ class SolverT final : public SolverBase {
     int rank_ = 0, world_ = 1;
     std::vector<int> h_part_;          // part of every mesh vertex (all ranks hold the same array)
     bool part_given_ = false;
-    DevBuf<int> d_part_of_, d_rowmap_, d_colmap_, d_node_of_col_, d_glob_of_col_, d_send_rows_, d_send_nodes_, d_push_tab_;
+    DevBuf<int> d_part_of_, d_rowmap_, d_colmap_, d_node_of_col_, d_glob_of_col_, d_send_rows_, d_send_nodes_, d_push_tab_, d_dir_nodes_;
+    int64_t n_dir_ = 0;                  // Dirichlet nodes (no unknown) of the whole mesh
     const int* rowmap_p_ = nullptr;      // per node: local row or -1
     const int* colmap_p_ = nullptr;      // per node: local column (row or ghost) or -1
     const int* node_of_col_p_ = nullptr; // per local column: mesh node
@@ -1542,7 +1698,9 @@ class SolverT final : public SolverBase {
     // persistent whole-solve kernel
     int pcg_max_grid_ = 0;
     int dual_max_grid_ = 0;
+    int bicg_max_grid_ = 0;
     int grid_cap_ = INT32_MAX;
+    int zigzag_ = 1;     // FEAB_ZIGZAG=0: phase B of the persistent kernels walks the rows ascending like the other phases
     bool dual_ = true;   // FEAB_DUAL=0 runs the two Gray-Scott solves one after the other
     bool dual_last_ = false;
     DevBuf<R> d_dpart_;
@@ -1552,6 +1710,14 @@ class SolverT final : public SolverBase {
     DevBuf<R> d_ppart_;
     cudaEvent_t ev_solve_[4] = {};
     bool time_solves_ = false, graph_mode_last_ = false;
+    // FEAB_STEP_PROF=1: device time of the pieces of the LAST step of a feab_step call (events on the solver stream):
+    // [0] upload (+ root push), [1] gather + RHS kernel, [2] solve kernels, [3] epilogue, [4] value broadcast, [5] download
+    bool step_prof_ = false, mark_now_ = false;
+    cudaEvent_t ev_ph_[8] = {};
+    double phase_ms_[6] = {0, 0, 0, 0, 0, 0};
+    void mark(int i) {
+        if (step_prof_ && mark_now_) cudaEventRecord(ev_ph_[i], stream_);
+    }
     double solve_ms_ = 0;
 
     double last_ms_ = 0;

@@ -116,6 +116,12 @@ __global__ void make_idx_map(const int* __restrict__ flag, const int* __restrict
     }
 }
 
+// nodes WITHOUT an unknown (Dirichlet boundary nodes), ascending: node i is the (i - excl[i])-th of them
+__global__ void make_dirichlet_list(const int* __restrict__ flag, const int* __restrict__ excl, int64_t V, int* __restrict__ dir_nodes) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < V && !flag[i]) dir_nodes[i - excl[i]] = (int)i;
+}
+
 // ------------------------------------------------------------------------------------------------
 // Row candidates: every triangle corner whose node owns a row contributes its unknown partner nodes.
 // An entry (i, j) of M/K exists iff some triangle holds both nodes and both pass the filter

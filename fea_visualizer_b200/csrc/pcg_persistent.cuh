@@ -44,6 +44,7 @@ struct PcgArgs {
                        // from the RHS kernel's published sums (mailbox all-reduce number ar_seq); 0: CgState is already set
     R tol;
     int maxit;
+    int zigzag;        // phase B walks the rows descending (L2 reuse across the phase boundaries); FEAB_ZIGZAG=0 switches it off
     unsigned long long* prof; // optional (FEAB_PCG_PROF=1): ns spent by CTA 0 in [A, sync1 (barrier + all-reduce of p.Ap), -, B, sync2, -, C, sync3, -], iterations
 };
 
@@ -318,9 +319,12 @@ __global__ void __launch_bounds__(ROWS, MINB) pcg_persistent(PcgArgs<R> a, Comm 
         // ---------------- phase B: r -= alpha y, |r|^2, r.z  (ConjugateGradient.h:67-76) --------------------------
         // x += alpha p is deferred to phase C, which reads p anyway (one vector read less per iteration; same
         // operations on the same operands, so the same bits).
+        // Rows are walked DESCENDING: the SpMV wrote y ascending, so its last rows are still in L2 here, and phase C
+        // (ascending) starts on the rows this phase touched last.
         const R alpha = abs_old / pap[0];
         R prr = (R)0, prz = (R)0;
-        for (int64_t i = gtid; i < nvec; i += gthreads) {
+        for (int64_t j = gtid; j < nvec; j += gthreads) {
+            const int64_t i = a.zigzag ? nvec - 1 - j : j;
             R rv[N], yv[N], dv[N];
             vload<R>(rs + i * N, rv);
             vload<R>(a.y + i * N, yv);

@@ -626,6 +626,82 @@ __global__ void __launch_bounds__(kBlock) finish_step(float* __restrict__ values
     }
 }
 
+// The same epilogue on a PARTITION: one pass over this rank's own rows (not over all V mesh nodes -- every rank would read the
+// whole rowmap and V / 256 CTAs would queue up at the ticket), bounded grid.  node_of_row[m] = mesh node of local row m.
+// Dirichlet nodes (no row anywhere) are zeroed by every rank from the list dir_nodes, like map_vector_to_surface does
+// (src/FEM/CPUSolver.cpp:28-36).  Boundary rows also go to the neighbours' ghosts; the last CTA raises the state flags.
+template <typename R>
+__global__ void __launch_bounds__(kBlock) finish_rows(float* __restrict__ values, const int* __restrict__ node_of_row, int64_t n,
+                                                      const int* __restrict__ dir_nodes, int64_t n_dir, R* __restrict__ u, R* __restrict__ v,
+                                                      int wave, R dt, int sol_is_v, int* __restrict__ unstable, int stamp, Comm cm,
+                                                      HaloPlan hp) {
+    if (comm_failed(cm)) return;  // fail closed: a solve that lost a peer writes nothing back
+    bool bad = false, pushed = false;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; m < n; m += stride) {
+        const int node = node_of_row[m];
+        R ui = u[m], vi = v[m];
+        if (wave) {
+            ui = Ops<R>::add(through_float(ui), Ops<R>::mul(vi, dt));
+            u[m] = ui;
+        }
+        const float out = (float)(sol_is_v ? vi : ui);
+        values[node] = out;
+        bad = bad || ui > (R)1e4f || vi > (R)1e4f;
+        if (m >= hp.n_int) {
+            const int* t = hp.push_tab + (size_t)(m - hp.n_int) * hp.nnb;
+            for (int b = 0; b < hp.nnb; b++) {
+                const int d = t[b];
+                if (d >= 0) {
+                    const int q = hp.nb_rank[b];
+                    reinterpret_cast<R*>(hp.base[q] + hp.off_vec[kVecU][q])[d] = ui;
+                    reinterpret_cast<R*>(hp.base[q] + hp.off_vec[kVecV][q])[d] = vi;
+                    reinterpret_cast<float*>(hp.base[q] + hp.off_vec[kVecValues][q])[node] = out;
+                    pushed = true;
+                }
+            }
+        }
+    }
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_dir; i += stride) values[dir_nodes[i]] = 0.0f;
+    if (__any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0) atomicMax(unstable, stamp);
+    __shared__ int s_last;
+    if (__syncthreads_or(pushed ? 1 : 0)) __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        s_last = atomicAdd(&cm.loc->ticket, 1u) == gridDim.x - 1 ? 1 : 0;
+    }
+    __syncthreads();
+    if (s_last && threadIdx.x == 0) {
+        cm.loc->ticket = 0;
+        __threadfence_system();
+        const unsigned long long s = cm.loc->state_seq + 1;
+        cm.loc->state_seq = s;
+        for (int b = 0; b < hp.nnb; b++) st_release_sys(&cm.ctrl[hp.nb_rank[b]]->state_flag[cm.rank], s);
+    }
+}
+
+// surface->values -> solver vector on a partition: one pass over this rank's columns (own rows + ghosts)
+template <typename R>
+__global__ void __launch_bounds__(kBlock) gather_cols(const float* __restrict__ values, const int* __restrict__ node_of_col, int64_t n_cols,
+                                                      R* __restrict__ x, Comm cm) {
+    if (comm_failed(cm)) return;
+    for (int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; m < n_cols; m += (int64_t)gridDim.x * blockDim.x) {
+        const int node = node_of_col[m];
+        if (node >= 0) x[m] = (R)values[node];
+    }
+}
+// FEAB_SYNC_ROOT on a peer: copy the surface values of this rank's columns (own rows + ghosts) from rank 0's mirror, read over
+// NVLink, into the local mirror (comm.cuh root_signal / root_wait order it after rank 0's upload)
+__global__ void __launch_bounds__(kBlock) pull_cols(const float* root_values, const int* __restrict__ node_of_col, int64_t n_cols,
+                                                    float* __restrict__ mirror, Comm cm) {
+    if (comm_failed(cm)) return;
+    for (int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; m < n_cols; m += (int64_t)gridDim.x * blockDim.x) {
+        const int node = node_of_col[m];
+        if (node >= 0) mirror[node] = root_values[node];
+    }
+}
+
 __global__ void brush_nodes(float* __restrict__ values, const long long* __restrict__ nodes, int64_t count, int64_t V, float strength) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < count && nodes[i] >= 0 && nodes[i] < V) values[nodes[i]] = strength;

@@ -247,7 +247,8 @@ class Feab:
         out = (C.c_double * 16)()
         self._ck(self.lib.feab_pcg_profile(self.h, out, C.c_int(1 if reset else 0)))
         names = ["spmv", "sync1", "unused1", "update", "sync2", "unused2", "direction", "sync3", "unused3"]
-        return {"ns": dict(zip(names, list(out)[:9])), "iterations": int(out[9])}
+        steps = ["upload", "gather_rhs", "solves", "epilogue", "broadcast", "download"]
+        return {"ns": dict(zip(names, list(out)[:9])), "iterations": int(out[9]), "step_ms": dict(zip(steps, list(out)[10:16]))}
 
     def device_info(self):
         sm, mem = C.c_int(), C.c_int64()

@@ -155,16 +155,18 @@ class ThreadedRanks(VirtualRanks):
         import threading
         errs = []
 
-        def run(h):
+        def run(r, h):
             try:
                 h.step(nsteps)
             except Exception as e:  # noqa: BLE001 - re-raised below
-                errs.append(e)
+                errs.append((r, e))
 
-        ts = [threading.Thread(target=run, args=(h,)) for h in self.hs]
+        ts = [threading.Thread(target=run, args=(r, h)) for r, h in enumerate(self.hs)]
         for t in ts:
             t.start()
         for t in ts:
             t.join()
         if errs:
-            raise errs[0]
+            if len(errs) == 1:
+                raise errs[0][1]
+            raise _feab.FeabError(getattr(errs[0][1], "code", -1), " || ".join(f"[rank {r}] {e}" for r, e in errs))

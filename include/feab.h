@@ -195,7 +195,9 @@ int feab_time_kernel(FeabHandle* h, int kernel, int reps, double* ms_per_launch,
  * persistent PCG kernel spent in [0] SpMV phase, [1] grid sync merged with the all-reduce of p.Ap, [3] update phase,
  * [4] grid sync merged with the all-reduce of |r|^2, r.z, [6] direction phase (incl. halo stores), [7] grid sync that
  * raises the halo flags; [2], [5], [8] unused (they were separate all-reduce / push stages before the syncs were merged);
- * [9] = iterations counted.  Zeros when profiling is off. */
+ * [9] = iterations counted.  Zeros when profiling is off.
+ * FEAB_STEP_PROF=1: [10..15] = device ms of the pieces of the LAST step of the last feab_step call (events on the solver
+ * stream): upload (+ root push), gather + RHS kernel, solve kernels, epilogue, value broadcast, download. */
 int feab_pcg_profile(FeabHandle* h, double* out16, int reset);
 int feab_device_info(const FeabHandle* h, int* sm_count, int64_t* total_mem_bytes, char* name64);
 

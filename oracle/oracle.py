@@ -188,6 +188,33 @@ class Reference(_Base):
         return int(f(C.c_int(n)))
 
 
+def eigen_bicgstab_available() -> bool:
+    return os.path.exists(os.path.join(HERE, "_ref", "libeigen_bicgstab.so"))
+
+
+def eigen_bicgstab(rowptr, col, val, b, tol_rel=None, max_iter=-1):
+    """Eigen's own BiCGSTAB<SparseMatrix<double>, DiagonalPreconditioner<double>> (lib/eigen, BiCGSTAB.h:32-119) on a CSR
+    system, x0 = 0, stopping on |r| <= tol_rel |b| (ref_bicgstab_harness.cpp).  Returns (x, iterations, error, info)."""
+    name = "libeigen_bicgstab.so"
+    if name not in _ref_libs:
+        _ref_libs[name] = C.CDLL(os.path.join(HERE, "_ref", name))
+    lib = _ref_libs[name]
+    rowptr = np.ascontiguousarray(rowptr, dtype=np.int32)
+    col = np.ascontiguousarray(col, dtype=np.int32)
+    val = np.ascontiguousarray(val, dtype=np.float64)
+    b = np.ascontiguousarray(b, dtype=np.float64)
+    n = len(b)
+    assert len(rowptr) == n + 1 and len(col) == len(val) == rowptr[-1]
+    x = np.zeros(n, np.float64)
+    it, err = C.c_int64(), C.c_double()
+    f = lib.eigen_bicgstab_solve
+    f.restype = C.c_int
+    info = f(C.c_int64(n), C.c_void_p(rowptr.ctypes.data), C.c_void_p(col.ctypes.data), C.c_void_p(val.ctypes.data),
+             C.c_void_p(b.ctypes.data), C.c_double(np.finfo(np.float64).eps if tol_rel is None else tol_rel), C.c_int64(max_iter),
+             C.c_void_p(x.ctypes.data), C.byref(it), C.byref(err))
+    return x, int(it.value), float(err.value), int(info)
+
+
 def csc_to_dense(n, outer, inner, val):
     a = np.zeros((n, n), dtype=val.dtype)
     for j in range(n):

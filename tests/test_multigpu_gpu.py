@@ -152,7 +152,9 @@ def test_virtual_ranks_fp32_and_multi_step_call():
     assert (A.get_state(0) == B.get_state(0)).all() and (A.get_state(1) == B.get_state(1)).all()
 
 
-def test_unconnected_partition_and_bicgstab_are_refused():
+def test_unconnected_partition_and_lockstep_bicgstab_are_refused():
+    """BiCGSTAB on a partition runs through the persistent kernel only (bicg_persistent.cuh has the halo exchange); the
+    lock-step group driver and the WHILE-graph kernels refuse it."""
     xyz, tri, ob = mesh("grid")
     h = feab.Feab(real=64)
     h.mg_config(0, 2)
@@ -163,6 +165,10 @@ def test_unconnected_partition_and_bicgstab_are_refused():
     G.set_equation(2)
     with pytest.raises(feab.FeabError):
         G.step(1)
+    T = threaded(2, 64, xyz, tri, ob, 0, solver=feab.SOLVER_BICGSTAB, loop_mode=feab.LOOP_GRAPH_WHILE)
+    T.set_equation(2)
+    with pytest.raises(feab.FeabError):
+        T.step(1)
 
 
 def test_one_process_per_gpu_partitioned_solve():
@@ -278,3 +284,30 @@ def test_threaded_ranks_rows_above_the_tile_staging_capacity(world):
 
         run_steps(G, V, eq, 4, per_step=check)
         assert worst[0] <= 1e-8, (eq, worst)
+
+
+@pytest.mark.parametrize("name,bc", [("disk14", 0), ("disk14", 1), ("ico12", 0)])
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_threaded_ranks_bicgstab_partitioned(name, bc, world):
+    """BASELINE config 4 ("non-symmetric solve, 1 and 2 B200"): the persistent BiCGSTAB kernel on a row partition -- y and z
+    halos pushed by the phases that produce them, five merged syncs per trip -- against the single-GPU run (summation order
+    only), the fp64 oracle in BiCGSTAB mode (1e-8 per step) and Eigen's own BiCGSTAB when it travelled with the snapshot."""
+    xyz, tri, ob = mesh(name)
+    V = len(xyz)
+    F = single(64, xyz, tri, ob, bc, solver=feab.SOLVER_BICGSTAB)
+    G = threaded(world, 64, xyz, tri, ob, bc, solver=feab.SOLVER_BICGSTAB)
+    D = O.Oracle(xyz, tri, ob, bc, real=64)
+    D.set_solver(mode=1)
+    ref, orc = [], []
+    run_steps(F, V, 2, 4, per_step=lambda s, X: ref.append((X.get_values(), X.get_state(0), X.stats()["iterations"][0])))
+    run_steps(D, V, 2, 4, per_step=lambda s, X: orc.append((X.get_values(), X.get_state(0))))
+    worst = [0.0, 0.0]
+
+    def check(s, X):
+        worst[0] = max(worst[0], rel_l2(X.get_state(0), ref[s][1]))
+        worst[1] = max(worst[1], rel_l2(X.get_state(0), orc[s][1]), rel_l2(X.get_values(), orc[s][0]))
+        assert abs(X.stats()["iterations"][0] - ref[s][2]) <= 2
+
+    run_steps(G, V, 2, 4, per_step=check)
+    assert worst[0] <= 1e-10, worst      # vs one GPU: summation order of the dot products (BiCGSTAB amplifies it more than CG)
+    assert worst[1] <= 1e-8, worst       # vs the fp64 oracle

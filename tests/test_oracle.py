@@ -236,3 +236,48 @@ def test_unit_sphere_gray_scott_blows_up_in_the_reference_itself():
         else:
             assert fired is None and peak <= 1.0, (fired, peak)
         R.close()
+
+
+def _advdiff_system(D, u0):
+    """A = M/dt + c K - Adv (src/FEM/CPUSolver.cpp:95) and b = (M/dt) u0 as fp64 CSR, from the oracle's own matrices."""
+    import scipy.sparse as sp
+    n = D.num_unknowns()
+    mats = [sp.csc_matrix((v.astype(np.float64), i, o), shape=(n, n)) for o, i, v in (D.csc(w) for w in range(3))]
+    dt, c = np.float64(np.float32(0.001)), np.float64(np.float32(0.25))
+    Md = mats[0] / dt
+    A = ((Md + c * mats[1]) - mats[2]).tocsr()
+    A.sort_indices()
+    return A, Md @ u0
+
+
+@pytest.mark.parametrize("name,bc", [("ico8d", 0), ("disk14", 0), ("disk14", 1), ("grid", 0)])
+def test_bicgstab_restatement_against_eigens_own_bicgstab(name, bc):
+    """the non-symmetric mode is checked against Eigen's BiCGSTAB<SparseMatrix<double>> (Jacobi
+    right-preconditioned, lib/eigen/Eigen/src/IterativeLinearSolvers/BiCGSTAB.h:32-119, compiled from the vendored tree into
+    oracle/_ref/libeigen_bicgstab.so).  Pins oracle mode 1 (fea_oracle_impl.h FN(bicgstab)): same iterates up to the
+    summation order of the dot products (Eigen reduces in SIMD packets), same iteration count within 1, both at eps."""
+    if not O.eigen_bicgstab_available():
+        pytest.skip("oracle/_ref/libeigen_bicgstab.so not built (needs /root/reference)")
+    xyz, tri = {**small_meshes(), "ico8d": meshes.icosphere(8, displace=True), "disk14": meshes.disk(14)}[name]
+    V = len(xyz)
+    ob = meshes.boundary_flags(V, tri)
+    D = O.Oracle(xyz, tri, ob, bc, real=64)
+    D.set_solver(mode=1)
+    D.set_equation(2)
+    vals = np.zeros(V, np.float32)
+    vals[meshes.seed_nodes(V)] = 1.0
+    idx = D.idx_map()
+    for step in range(3):
+        u0 = np.zeros(D.num_unknowns())
+        u0[idx[idx >= 0]] = vals[idx >= 0].astype(np.float64)
+        A, b = _advdiff_system(D, u0)
+        x, it, err, info = O.eigen_bicgstab(A.indptr, A.indices, A.data, b)
+        D.set_values(vals)
+        D.step(1)
+        mine = D.get_state(0)
+        oit, oerr = D.last_stats()
+        assert err <= 2.3e-16 and oerr[0] <= 2.3e-16        # info() compares error() with the ABSOLUTE tolerance: not used
+        assert rel_l2(mine, x) <= 1e-12, (step, rel_l2(mine, x))
+        assert abs(int(oit[0]) - it) <= 1, (oit, it)
+        assert np.linalg.norm(b - A @ x) / np.linalg.norm(b) <= 1e-13
+        vals = D.get_values()

@@ -476,3 +476,43 @@ def test_rows_above_the_tile_staging_capacity(name, bc, eq, loop):
     assert worst[0] <= FP64_STEP_TOL, worst[0]
     if eq == 3 and loop == feab.LOOP_PERSISTENT:
         assert F.stats()["shared_iterations"] > 0          # the lock-step kernel ran these tiles
+
+
+# ---------------------------------------------------------------------------------------------- BiCGSTAB vs Eigen's own
+@pytest.mark.parametrize("name,bc", [("ico8d", 0), ("disk14", 0), ("disk14", 1), ("fan_grid40x30", 0)])
+@pytest.mark.parametrize("loop", [feab.LOOP_PERSISTENT, feab.LOOP_GRAPH_WHILE, feab.LOOP_HOST_BATCHED])
+def test_bicgstab_mode_against_eigens_own_bicgstab(name, bc, loop):
+    """The non-symmetric solver mode against Eigen's BiCGSTAB<SparseMatrix<double>> (BiCGSTAB.h:32-119, compiled from the
+    vendored lib/eigen into oracle/_ref/libeigen_bicgstab.so) on the fp64 operator built from the matrices feab_get_csr
+    exports: A = M/dt + c K - Adv, b = (M/dt) u.  Bar: 1e-10 relative L2 on the solution of each of 3 steps, iteration
+    counts within 4, true residual <= 1e-12.  All three loop drivers: the persistent whole-solve kernel (bicg_persistent.cuh)
+    and the multi-kernel WHILE graph / host-batched loop (bicgstab.cuh)."""
+    import scipy.sparse as sp
+    if not O.eigen_bicgstab_available():
+        pytest.skip("oracle/_ref/libeigen_bicgstab.so did not travel with the snapshot")
+    xyz, tri = _fan_cases()[name] if name.startswith("fan") else cases()[name]
+    V = len(xyz)
+    ob = meshes.boundary_flags(V, tri)
+    F = make(64, xyz, tri, ob, bc, solver=feab.SOLVER_BICGSTAB, assembly=feab.ASSEMBLY_ORDERED, loop_mode=loop)
+    n = F.num_unknowns()
+    mats = [sp.csr_matrix((v, c, r), shape=(n, n)) for r, c, v in (F.csr(w) for w in range(3))]
+    dt, c = np.float64(np.float32(0.001)), np.float64(np.float32(0.25))
+    Md = mats[0] / dt
+    A = ((Md + c * mats[1]) - mats[2]).tocsr()
+    A.sort_indices()
+    idx = F.idx_map()
+    vals = np.zeros(V, np.float32)
+    vals[meshes.seed_nodes(V)] = 1.0
+    F.clear()
+    F.set_equation(2)
+    for step in range(3):
+        u0 = np.zeros(n)
+        u0[idx[idx >= 0]] = vals[idx >= 0].astype(np.float64)
+        b = Md @ u0
+        x, it, err, info = O.eigen_bicgstab(A.indptr, A.indices, A.data, b)
+        F.step(1, values=vals, sync_values=True)
+        got = F.get_state(0)
+        st = F.stats()
+        assert err <= 2.3e-16 and rel_l2(got, x) <= 1e-10, (step, err, rel_l2(got, x))   # info() compares error() with the ABSOLUTE tolerance: not used
+        assert abs(st["iterations"][0] - it) <= 4, (st["iterations"], it)   # BiCGSTAB's residual is not monotone: the crossing of eps moves by a few trips with the summation order
+        assert np.linalg.norm(b - A @ got) / np.linalg.norm(b) <= 1e-12
