@@ -20,6 +20,7 @@
 #include "common.cuh"
 #include "partition.cuh"
 #include "pattern.cuh"
+#include "pcg_cluster.cuh"
 #include "pcg_persistent.cuh"
 #include "pcg_dual.cuh"
 #include "rhs_tma.cuh"
@@ -82,6 +83,7 @@ static inline int cdiv64(int64_t a, int64_t b) { return (int)((a + b - 1) / b); 
 struct SolverBase {
     virtual ~SolverBase() {}
     virtual void set_mesh(int64_t V, const float* xyz, int64_t T, const uint32_t* tri, const uint8_t* onb) = 0;
+    virtual void set_mesh_ex(int64_t V, const float* xyz, int64_t T, const uint32_t* tri, const uint8_t* onb, int bc, const float* vel) = 0;
     virtual void set_bc(int bc) = 0;
     virtual void assemble(const float* vel) = 0;
     virtual void get_counts(int64_t* V, int64_t* n, int64_t* nnz, int* maxrow) = 0;
@@ -110,6 +112,7 @@ struct SolverBase {
     virtual void mg_connect(int peer, const FeabMgExport* e, int same_process) = 0;
     virtual void mg_get_layout(int64_t* n_own, int64_t* n_int, int64_t* n_ghost, int64_t* n_cols) = 0;
     virtual void mg_get_maps(int32_t* row_node, int32_t* col_unknown) = 0;
+    virtual void mg_get_partition(int32_t* part) = 0;
     // lock-step driving (feab_mg_group_step)
     enum { LS_PUSH_STATE, LS_BEGIN, LS_COLLECT, LS_CG_BEGIN, LS_SPMV, LS_UPDATE, LS_DIRECTION, LS_FINISH };
     virtual cudaStream_t ls_prepare(cudaStream_t shared) = 0;
@@ -213,6 +216,34 @@ class SolverT final : public SolverBase {
         CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bocc, bicg_persistent<R, kPcgRows, kPcgCpr, kPcgStages, kPcgMinB>, kPcgRows,
                                                          PCfg::kSmemBytes));
         bicg_max_grid_ = coop ? bocc * sms_ : 0;
+        // small meshes: whole time steps inside one thread-block cluster (pcg_cluster.cuh); FEAB_CLUSTER=0 switches it off
+        {
+            const int smem = kClusterSmemBudget;
+            if (const char* v = getenv("FEAB_CLUSTER_THREADS")) cluster_threads_ = atoi(v) == 1024 ? 1024 : 512;
+            bool ok = true;
+            for (const void* f : {(const void*)pcg_cluster<R, 1024>, (const void*)pcg_cluster<R, 512>}) {
+                ok = ok && cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) == cudaSuccess;
+                ok = ok && cudaFuncSetAttribute(f, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess;
+            }
+            for (int cs = kClusterMaxCtas; ok && cs >= 2 && cluster_ctas_ == 0; cs /= 2) {
+                cudaLaunchConfig_t cfg = {};
+                cfg.gridDim = dim3(cs);
+                cfg.blockDim = dim3(1024);
+                cfg.dynamicSmemBytes = smem;
+                cudaLaunchAttribute at[1];
+                at[0].id = cudaLaunchAttributeClusterDimension;
+                at[0].val.clusterDim.x = cs;
+                at[0].val.clusterDim.y = 1;
+                at[0].val.clusterDim.z = 1;
+                cfg.attrs = at;
+                cfg.numAttrs = 1;
+                int nclusters = 0;
+                if (cudaOccupancyMaxActiveClusters(&nclusters, pcg_cluster<R, 1024>, &cfg) == cudaSuccess && nclusters >= 1) cluster_ctas_ = cs;
+            }
+            cudaGetLastError();
+            if (const char* v = getenv("FEAB_CLUSTER"))
+                if (atoi(v) == 0) cluster_ctas_ = 0;
+        }
         // CUDA loads kernels lazily, on their first launch, and that load may wait for the device to drain.  A partitioned
         // step launches kernels while kernels of other ranks SPIN on flags this rank has yet to raise; if the launch that
         // raises them is a first launch, the load and the spin wait for each other (seen with several ranks in one process).
@@ -268,6 +299,8 @@ class SolverT final : public SolverBase {
         touch(pcg_persistent<R, kPcgRows, kPcgCpr, kPcgStages, kPcgMinB>);
         touch(pcg_dual<R, kDualRows, kPcgCpr, kPcgStages, kPcgMinB>);
         touch(bicg_persistent<R, kPcgRows, kPcgCpr, kPcgStages, kPcgMinB>);
+        touch(pcg_cluster<R, 1024>);
+        touch(pcg_cluster<R, 512>);
     }
 
     // ---- SpMV variants: 0 = LDG/CSR-stream (solver.cuh), 1.. = TMA pipelines (spmv_tma.cuh) ----
@@ -346,16 +379,7 @@ class SolverT final : public SolverBase {
         CK(cudaSetDevice(device_));
         REQUIRE(V > 0 && T >= 0 && xyz && onb && (T == 0 || tri), FEAB_EINVAL, "set_mesh: bad arguments");
         REQUIRE(V < (int64_t)INT32_MAX && 9 * T < (int64_t)INT32_MAX, FEAB_EINVAL, "set_mesh: mesh too large for int32 indexing");
-        // validate triangle indices on the host copy (the reference would index out of bounds)
-        for (int64_t i = 0; i < 3 * T; i++) REQUIRE(tri[i] < (uint64_t)V, FEAB_EINVAL, "set_mesh: triangle index out of range");
-        if (world_ > 1) {
-            if (part_given_) {
-                REQUIRE((int64_t)h_part_.size() == V, FEAB_EINVAL, "set_mesh: partition array length != num_vertices");
-            } else {  // default partition: recursive coordinate bisection, identical on every rank
-                h_part_.assign((size_t)V, 0);
-                rcb_partition(V, xyz, world_, h_part_.data());
-            }
-        }
+        if (world_ > 1 && part_given_) REQUIRE((int64_t)h_part_.size() == V, FEAB_EINVAL, "set_mesh: partition array length != num_vertices");
         V_ = V;
         T_ = T;
         d_xyz_.alloc(3 * V);
@@ -364,15 +388,124 @@ class SolverT final : public SolverBase {
         CK(cudaMemcpyAsync(d_xyz_.p, xyz, 3 * V * sizeof(float), cudaMemcpyHostToDevice, stream_));
         if (T) CK(cudaMemcpyAsync(d_tri_.p, tri, 3 * T * sizeof(uint32_t), cudaMemcpyHostToDevice, stream_));
         CK(cudaMemcpyAsync(d_onb_.p, onb, V, cudaMemcpyHostToDevice, stream_));
+        // validate the triangle indices (the reference would index out of bounds) on the device copy: no host pass over 3 T indices
+        CK(cudaMemsetAsync(d_unstable_, 0, sizeof(int), stream_));
+        if (T) validate_indices<<<std::max(1, std::min(cdiv64(3 * T, kBlock), sms_ * 8)), kBlock, 0, stream_>>>(d_tri_.p, 3 * T, (uint32_t)V, d_unstable_);
+        int bad_index = 0;
+        CK(cudaMemcpyAsync(&bad_index, d_unstable_, sizeof(int), cudaMemcpyDeviceToHost, stream_));
+        CK(cudaStreamSynchronize(stream_));
+        if (bad_index) {
+            have_mesh_ = false;
+            CK(cudaMemsetAsync(d_unstable_, 0, sizeof(int), stream_));
+            throw Err{FEAB_EINVAL, "set_mesh: triangle index out of range"};
+        }
         if (world_ > 1) {
             d_part_of_.alloc(V);
-            CK(cudaMemcpyAsync(d_part_of_.p, h_part_.data(), V * sizeof(int), cudaMemcpyHostToDevice, stream_));
+            if (part_given_)
+                CK(cudaMemcpyAsync(d_part_of_.p, h_part_.data(), V * sizeof(int), cudaMemcpyHostToDevice, stream_));
+            else  // default partition: recursive coordinate bisection on the device, identical on every rank (partition.cuh)
+                rcb_device(world_);
         }
         CK(cudaStreamSynchronize(stream_));
         have_mesh_ = true;
         symbolic();
         assemble(nullptr);
         clear();
+    }
+
+    // d_part_of_ = recursive coordinate bisection of d_xyz_ into `parts` pieces; == rcb_partition() on the host, bit for bit
+    void rcb_device(int parts) {
+        const int64_t V = V_;
+        struct Seg {
+            int label, parts;
+            long long count;
+        };
+        std::vector<Seg> segs = {{0, parts, (long long)V}};
+        CK(cudaMemsetAsync(d_part_of_.p, 0, V * sizeof(int), stream_));
+        DevBuf<unsigned> box, hist;
+        DevBuf<int> flag, rank;
+        box.alloc(kMaxRanks * 6);
+        hist.alloc(kMaxRanks / 2 * 256);
+        flag.alloc(V);
+        rank.alloc(V + 1);
+        const int gS = std::max(1, std::min(cdiv64(V, kBlock), sms_ * 8)), gV = cdiv64(V, kBlock);
+        while (true) {
+            RcbLevel lv;
+            std::memset(&lv, 0, sizeof(lv));
+            for (int q = 0; q < kMaxRanks; q++) lv.seg_of_label[q] = -1;
+            std::vector<int> act;
+            for (int i = 0; i < (int)segs.size() && (int)act.size() < kMaxRanks / 2; i++)
+                if (segs[i].parts > 1) act.push_back(i);
+            if (act.empty()) break;
+            lv.nseg = (int)act.size();
+            long long k[kMaxRanks] = {}, nl[kMaxRanks] = {};
+            for (int a = 0; a < lv.nseg; a++) {
+                const Seg& sg = segs[act[a]];
+                lv.label[a] = sg.label;
+                lv.seg_of_label[sg.label] = a;
+                lv.right_label[a] = sg.label + sg.parts / 2;
+                nl[a] = sg.count * (sg.parts / 2) / sg.parts;
+                k[a] = nl[a] - 1;
+            }
+            // widest axis of every segment (ties: the lowest axis, like the host's strict comparison)
+            unsigned hbox[kMaxRanks * 6];
+            for (int i = 0; i < lv.nseg * 6; i++) hbox[i] = (i % 6) < 3 ? 0xffffffffu : 0u;
+            CK(cudaMemcpyAsync(box.p, hbox, lv.nseg * 6 * sizeof(unsigned), cudaMemcpyHostToDevice, stream_));
+            rcb_bbox<<<gS, kBlock, 0, stream_>>>(d_xyz_.p, d_part_of_.p, V, lv, box.p);
+            CK(cudaMemcpyAsync(hbox, box.p, lv.nseg * 6 * sizeof(unsigned), cudaMemcpyDeviceToHost, stream_));
+            CK(cudaStreamSynchronize(stream_));
+            for (int a = 0; a < lv.nseg; a++) {
+                int axis = 0;
+                float ext[3];
+                for (int d = 0; d < 3; d++) ext[d] = rcb_unkey(hbox[a * 6 + 3 + d]) - rcb_unkey(hbox[a * 6 + d]);
+                for (int d = 1; d < 3; d++)
+                    if (ext[d] > ext[axis]) axis = d;
+                lv.axis[a] = axis;
+            }
+            // radix select of the (nl - 1)-th smallest coordinate key of every segment, 8 bits per pass
+            for (int shift = 24; shift >= 0; shift -= 8) {
+                CK(cudaMemsetAsync(hist.p, 0, lv.nseg * 256 * sizeof(unsigned), stream_));
+                rcb_hist<<<gS, kBlock, 0, stream_>>>(d_xyz_.p, d_part_of_.p, V, lv, shift, hist.p);
+                unsigned hh[kMaxRanks / 2 * 256];
+                CK(cudaMemcpyAsync(hh, hist.p, lv.nseg * 256 * sizeof(unsigned), cudaMemcpyDeviceToHost, stream_));
+                CK(cudaStreamSynchronize(stream_));
+                for (int a = 0; a < lv.nseg; a++) {
+                    if (nl[a] <= 0) continue;
+                    long long cum = 0;
+                    int d = 0;
+                    for (; d < 255; d++) {
+                        if (cum + hh[a * 256 + d] > k[a]) break;
+                        cum += hh[a * 256 + d];
+                    }
+                    k[a] -= cum;
+                    lv.prefix[a] |= (unsigned)d << shift;
+                }
+            }
+            for (int a = 0; a < lv.nseg; a++) {
+                lv.key[a] = nl[a] > 0 ? lv.prefix[a] : 0u;
+                lv.take[a] = nl[a] > 0 ? (int)(k[a] + 1) : 0;   // ties at the selected coordinate that stay on the left, by vertex index
+            }
+            for (int a = 0; a < lv.nseg; a++) {
+                rcb_tie_flags<<<gV, kBlock, 0, stream_>>>(d_xyz_.p, d_part_of_.p, V, lv, a, flag.p);
+                exclusive_scan(flag.p, V, rank.p, nullptr);
+                rcb_assign<<<gV, kBlock, 0, stream_>>>(d_xyz_.p, d_part_of_.p, V, lv, a, rank.p);
+            }
+            launches_ += 6 + 2 * lv.nseg;
+            CK(cudaGetLastError());
+            for (int a = 0; a < lv.nseg; a++) {
+                const Seg sg = segs[act[a]];
+                const int pl = sg.parts / 2;
+                segs[act[a]] = {sg.label, pl, nl[a]};
+                segs.push_back({sg.label + pl, sg.parts - pl, sg.count - nl[a]});
+            }
+        }
+    }
+
+    void set_mesh_ex(int64_t V, const float* xyz, int64_t T, const uint32_t* tri, const uint8_t* onb, int bc, const float* vel) override {
+        REQUIRE(bc == 0 || bc == 1, FEAB_EINVAL, "set_mesh_ex: bc must be 0 or 1");
+        bc_ = bc;  // taken by the symbolic pass / the assembly that set_mesh runs
+        if (vel) std::memcpy(vel_, vel, 3 * sizeof(float));
+        set_mesh(V, xyz, T, tri, onb);
     }
 
     void set_bc(int bc) override {
@@ -507,6 +640,7 @@ class SolverT final : public SolverBase {
 
     void symbolic() {
         drop_graphs();
+        cluster_ent_key_ = -1;
         op_valid_ = false;
         close_peers();
         const int64_t V = V_, T = T_;
@@ -524,11 +658,10 @@ class SolverT final : public SolverBase {
         make_idx_map<<<gV, kBlock, 0, stream_>>>(flag.p, excl.p, V, d_idx_.p, d_node_of_.p);
         launches_ += 2;
         n_dir_ = V - nglob_;
-        if (world_ > 1) {  // the partitioned epilogue walks rows, not nodes: it needs the Dirichlet nodes as a list
-            d_dir_nodes_.alloc(std::max<int64_t>(n_dir_, 1));
-            make_dirichlet_list<<<gV, kBlock, 0, stream_>>>(flag.p, excl.p, V, d_dir_nodes_.p);
-            launches_++;
-        }
+        // epilogues that walk rows instead of nodes (partitioned finish_rows, pcg_cluster) need the Dirichlet nodes as a list
+        d_dir_nodes_.alloc(std::max<int64_t>(n_dir_, 1));
+        make_dirichlet_list<<<gV, kBlock, 0, stream_>>>(flag.p, excl.p, V, d_dir_nodes_.p);
+        launches_++;
         if (world_ > 1) {
             number_partition();
         } else {
@@ -1119,6 +1252,95 @@ class SolverT final : public SolverBase {
         launches_ += 1;
     }
 
+    // Small meshes on one GPU with the persistent loop driver: all steps of the call in one cluster launch (pcg_cluster.cuh)
+    bool use_cluster() const {
+        return cluster_ctas_ > 0 && world_ == 1 && !lockstep_ && opt_.loop_mode == FEAB_LOOP_PERSISTENT && !use_bicgstab() && n_ > 0 &&
+               n_ <= (int64_t)cluster_ctas_ * kClusterMaxRowsPerCta;
+    }
+    void launch_cluster_steps(int nsteps) {
+        const R* A[2];
+        const R* dinv[2];
+        R* x[2];
+        solves(A, dinv, x);
+        if (values_dirty_) {  // somebody else wrote surface->values since the last step
+            R* target = eq_ == FEAB_EQ_REACTION_DIFFUSION ? d_v_.p : d_u_.p;
+            gather_values<R><<<cdiv64(V_, kBlock), kBlock, 0, stream_>>>(d_values_.p, colmap_p_, V_, target, cm_, hp_);
+            launches_++;
+            values_dirty_ = false;
+        }
+        const int C = (int)std::min<int64_t>(cluster_ctas_, std::max<int64_t>(1, (n_ + 511) / 512));
+        const int rpc = (int)((n_ + C - 1) / C);
+        if (cluster_ent_key_ != n_ * 32 + C) {  // most entries any CTA's row block holds: sizes the shared-memory copy of the matrix
+            std::vector<int> rp(C + 1);
+            for (int q = 0; q <= C; q++)
+                CK(cudaMemcpyAsync(&rp[q], d_rowptr_.p + std::min<int64_t>(n_, (int64_t)q * rpc), sizeof(int), cudaMemcpyDeviceToHost, stream_));
+            CK(cudaStreamSynchronize(stream_));
+            cluster_ent_max_ = 0;
+            for (int q = 0; q < C; q++) cluster_ent_max_ = std::max(cluster_ent_max_, rp[q + 1] - rp[q]);
+            cluster_ent_max_ = (cluster_ent_max_ + 1) & ~1;
+            cluster_ent_key_ = n_ * 32 + C;
+        }
+        const size_t base = (size_t)5 * rpc * sizeof(R) + (size_t)(rpc + 2) * sizeof(int);
+        int col_cap = 0, val_cap = 0;
+        if (base + (size_t)cluster_ent_max_ * (sizeof(int) + sizeof(R)) <= (size_t)kClusterSmemBudget)
+            col_cap = val_cap = cluster_ent_max_;
+        else if (base + (size_t)cluster_ent_max_ * sizeof(int) <= (size_t)kClusterSmemBudget)
+            col_cap = cluster_ent_max_;
+        ClusterArgs<R> ca;
+        ca.rowptr = d_rowptr_.p;
+        ca.col = d_col_.p;
+        ca.Md = d_Md_.p;
+        ca.Kv = d_K_.p;
+        for (int s = 0; s < 2; s++) {
+            ca.A[s] = A[s];
+            ca.dinv[s] = dinv[s];
+            ca.r[s] = d_r_[s].p;
+        }
+        ca.u = d_u_.p;
+        ca.v = d_v_.p;
+        ca.p = d_p_[0].p;
+        ca.values = d_values_.p;
+        ca.node_of = node_of_col_p_;
+        ca.dir_nodes = d_dir_nodes_.p;
+        ca.n_dir = n_dir_;
+        ca.n = n_;
+        ca.eq = eq_;
+        ca.sc = scalars();
+        ca.tol = tol();
+        ca.maxit = maxit();
+        ca.nsteps = nsteps;
+        ca.st = d_st_;
+        ca.unstable = d_unstable_;
+        if ((int64_t)step_stamp_ + nsteps >= INT32_MAX - 1) step_stamp_ = 0;
+        ca.stamp0 = step_stamp_ + 1;
+        ca.col_cap = col_cap;
+        ca.prof = prof_dual_ ? nullptr : d_prof_;
+        ca.val_cap = val_cap;
+        step_stamp_ += nsteps;
+        last_stamp_ = step_stamp_;
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(C);
+        cfg.blockDim = dim3(cluster_threads_);
+        cfg.dynamicSmemBytes = base + (size_t)val_cap * sizeof(R) + (size_t)col_cap * sizeof(int);
+        cfg.stream = stream_;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = C;
+        at[0].val.clusterDim.y = 1;
+        at[0].val.clusterDim.z = 1;
+        cfg.attrs = at;
+        cfg.numAttrs = 1;
+        CK(cudaEventRecord(ev_solve_[0], stream_));
+        if (cluster_threads_ == 512)
+            CK(cudaLaunchKernelEx(&cfg, pcg_cluster<R, 512>, ca));
+        else
+            CK(cudaLaunchKernelEx(&cfg, pcg_cluster<R, 1024>, ca));
+        CK(cudaEventRecord(ev_solve_[1], stream_));
+        launches_ += 1;
+        cluster_steps_last_ = nsteps;
+        dual_last_ = false;
+    }
+
     // num_solves: solves of this step (the first one takes the start of all of them, see launch_pcg_persistent)
     void enqueue_pcg(int slot, const R* const* Aall, const R* const* dinvall, R* const* xall, bool capturing, int num_solves = 1) {
         const R* A = Aall[slot];
@@ -1306,7 +1528,16 @@ class SolverT final : public SolverBase {
                 last_stamp_ = 1;     // ... and one instability stamp (the graph resets the flag at its head)
             }
             if (graph_mode && (!graph_exec_ || graph_eq_ != eq_)) build_graph();
-            for (int s = 0; s < nsteps; s++) {
+            cluster_steps_last_ = 0;
+            if (!graph_mode && use_cluster()) {
+                mark_now_ = true;
+                mark(1);
+                mark(2);
+                launch_cluster_steps(nsteps);
+                mark(3);
+                mark(4);
+            }
+            for (int s = 0; s < nsteps && cluster_steps_last_ == 0; s++) {
                 time_solves_ = !graph_mode && opt_.loop_mode == FEAB_LOOP_PERSISTENT && s == nsteps - 1;
                 mark_now_ = !graph_mode && s == nsteps - 1;
                 if (graph_mode) {
@@ -1346,6 +1577,11 @@ class SolverT final : public SolverBase {
         last_steps_ = nsteps;
         if (n_ > 0 && nsteps > 0 && graph_mode_last_) account_graph_launches(nsteps);
         solve_ms_ = 0;
+        if (cluster_steps_last_ > 0) {  // the cluster kernel holds whole steps: its time per step
+            float t = 0;
+            if (cudaEventElapsedTime(&t, ev_solve_[0], ev_solve_[1]) == cudaSuccess) solve_ms_ = t / cluster_steps_last_;
+            cudaGetLastError();
+        }
         if (time_solves_) {  // device time of the last step's persistent PCG kernels
             const int ns = eq_ == FEAB_EQ_REACTION_DIFFUSION && !dual_applies(false) ? 2 : 1;  // the dual path brackets both solves with one pair
             for (int sl = 0; sl < ns; sl++) {
@@ -1572,6 +1808,14 @@ class SolverT final : public SolverBase {
         if (n_ghost) *n_ghost = n_ghost_;
         if (n_cols) *n_cols = n_cols_;
     }
+    void mg_get_partition(int32_t* part) override {
+        REQUIRE(have_mesh_ && part, FEAB_ENOMESH, "mg_get_partition: no mesh");
+        CK(cudaSetDevice(device_));
+        if (world_ > 1)
+            CK(cudaMemcpy(part, d_part_of_.p, V_ * sizeof(int), cudaMemcpyDeviceToHost));
+        else
+            std::memset(part, 0, V_ * sizeof(int));
+    }
     void mg_get_maps(int32_t* row_node, int32_t* col_unknown) override {
         REQUIRE(have_mesh_, FEAB_ENOMESH, "mg_get_maps: no mesh");
         CK(cudaSetDevice(device_));
@@ -1699,8 +1943,13 @@ class SolverT final : public SolverBase {
     int pcg_max_grid_ = 0;
     int dual_max_grid_ = 0;
     int bicg_max_grid_ = 0;
+    int cluster_ctas_ = 0;      // largest cluster size pcg_cluster can be launched with (0: not available / switched off)
+    int cluster_steps_last_ = 0;
+    int cluster_threads_ = 512;   // 16 warps per CTA and 128 registers per thread measured faster than 1024 x 64 (FEAB_CLUSTER_THREADS=1024)
+    int64_t cluster_ent_key_ = -1;
+    int cluster_ent_max_ = 0;
     int grid_cap_ = INT32_MAX;
-    int zigzag_ = 1;     // FEAB_ZIGZAG=0: phase B of the persistent kernels walks the rows ascending like the other phases
+    int zigzag_ = 1;     // FEAB_ZIGZAG=0: phase C of the persistent kernels walks the rows ascending (boundary rows and their NVLink pushes last)
     bool dual_ = true;   // FEAB_DUAL=0 runs the two Gray-Scott solves one after the other
     bool dual_last_ = false;
     DevBuf<R> d_dpart_;
@@ -1876,6 +2125,9 @@ const char* feab_last_error(const FeabHandle* h) { return h ? h->err.c_str() : g
 int feab_set_mesh(FeabHandle* h, int64_t V, const float* xyz, int64_t T, const uint32_t* tri, const uint8_t* onb) {
     FEAB_TRY(h, h->impl->set_mesh(V, xyz, T, tri, onb));
 }
+int feab_set_mesh_ex(FeabHandle* h, int64_t V, const float* xyz, int64_t T, const uint32_t* tri, const uint8_t* onb, int bc, const float* vel) {
+    FEAB_TRY(h, h->impl->set_mesh_ex(V, xyz, T, tri, onb, bc, vel));
+}
 int feab_set_boundary_condition(FeabHandle* h, int bc) { FEAB_TRY(h, h->impl->set_bc(bc)); }
 int feab_assemble(FeabHandle* h, const float* velocity3) { FEAB_TRY(h, h->impl->assemble(velocity3)); }
 int feab_get_counts(const FeabHandle* h, int64_t* V, int64_t* n, int64_t* nnz, int* maxrow) {
@@ -1937,6 +2189,7 @@ int feab_mg_get_layout(FeabHandle* h, int64_t* n_own, int64_t* n_int, int64_t* n
     FEAB_TRY(h, h->impl->mg_get_layout(n_own, n_int, n_ghost, n_cols));
 }
 int feab_mg_get_maps(FeabHandle* h, int32_t* row_node, int32_t* col_unknown) { FEAB_TRY(h, h->impl->mg_get_maps(row_node, col_unknown)); }
+int feab_mg_get_partition(FeabHandle* h, int32_t* part) { FEAB_TRY(h, h->impl->mg_get_partition(part)); }
 
 static void group_step_impl(FeabHandle** hs, int count, int nsteps) {
     FeabHandle* h0 = hs[0];

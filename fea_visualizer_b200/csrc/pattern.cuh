@@ -116,6 +116,12 @@ __global__ void make_idx_map(const int* __restrict__ flag, const int* __restrict
     }
 }
 
+__global__ void validate_indices(const uint32_t* __restrict__ idx, int64_t count, uint32_t limit, int* __restrict__ bad) {
+    bool b = false;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += (int64_t)gridDim.x * blockDim.x) b = b || idx[i] >= limit;
+    if (b) *bad = 1;
+}
+
 // nodes WITHOUT an unknown (Dirichlet boundary nodes), ascending: node i is the (i - excl[i])-th of them
 __global__ void make_dirichlet_list(const int* __restrict__ flag, const int* __restrict__ excl, int64_t V, int* __restrict__ dir_nodes) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;

@@ -257,41 +257,40 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a, Com
         DUAL_STAMP(1)
 
         // ---------------- phase B (both systems): r -= alpha y, |r|^2, r.z ----------------
-        // Rows are walked DESCENDING and both systems are handled per row block: the SpMV wrote y ascending, so its last rows
-        // are still in L2 when this phase starts, and phase C (ascending) starts on the rows this phase touched last.  With two
-        // systems' vectors (10 x n reals) larger than the L2 this is what keeps r, D^-1 and y from being re-read from HBM.
         R alpha[2];
-        R pb[4] = {(R)0, (R)0, (R)0, (R)0};  // |r_0|^2, |r_1|^2, r_0.z_0, r_1.z_1 of this CTA
-        alpha[0] = abs_old[0] / pap[0];
-        alpha[1] = abs_old[1] / pap[1];
-        for (int64_t j = gtid; j < nvec; j += gthreads) {
-            const int64_t i = a.zigzag ? nvec - 1 - j : j;
+        R pb[4];  // |r_0|^2, |r_1|^2, r_0.z_0, r_1.z_1 of this CTA
 #pragma unroll
-            for (int s = 0; s < 2; s++) {
+        for (int s = 0; s < 2; s++) {
+            alpha[s] = abs_old[s] / pap[s];
+            R prr = (R)0, prz = (R)0;
+            R* const rs = a.r[s];
+            const R* const ys = a.y[s];
+            const R* const ds = a.dinv[s];
+            for (int64_t i = gtid; i < nvec; i += gthreads) {
                 R rv[N], yv[N], dv[N];
-                vload<R>(a.r[s] + i * N, rv);
-                vload_cs<R>(a.y[s] + i * N, yv);
-                vload<R>(a.dinv[s] + i * N, dv);
+                vload<R>(rs + i * N, rv);
+                vload_cs<R>(ys + i * N, yv);
+                vload<R>(ds + i * N, dv);
 #pragma unroll
                 for (int q = 0; q < N; q++) {
                     rv[q] = O::sub(rv[q], O::mul(alpha[s], yv[q]));
                     R z = O::mul(dv[q], rv[q]);
-                    pb[s] += rv[q] * rv[q];
-                    pb[2 + s] += rv[q] * z;
+                    prr += rv[q] * rv[q];
+                    prz += rv[q] * z;
                 }
-                vstore<R>(a.r[s] + i * N, rv);
+                vstore<R>(rs + i * N, rv);
             }
-        }
-        if (blockIdx.x == 0) {
-#pragma unroll
-            for (int s = 0; s < 2; s++)
+            if (blockIdx.x == 0) {
                 for (int64_t i = nvec * N + threadIdx.x; i < n; i += blockDim.x) {
-                    R rn = O::sub(a.r[s][i], O::mul(alpha[s], a.y[s][i]));
-                    a.r[s][i] = rn;
-                    R z = O::mul(a.dinv[s][i], rn);
-                    pb[s] += rn * rn;
-                    pb[2 + s] += rn * z;
+                    R rn = O::sub(rs[i], O::mul(alpha[s], ys[i]));
+                    rs[i] = rn;
+                    R z = O::mul(ds[i], rn);
+                    prr += rn * rn;
+                    prz += rn * z;
                 }
+            }
+            pb[s] = prr;
+            pb[2 + s] = prz;
         }
         block_sum_vec<R, 4, NWT>(pb, red);
         DUAL_STAMP(3)
@@ -308,45 +307,51 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a, Com
         const bool first = it == 1;  // x0 = 0 is never stored: the first update writes 0 + alpha p
         bool pushed = false;
         // ---------------- stopping tests (ConjugateGradient.h:72-73), per system; direction update for the ones that go on ----
-        R beta[2] = {(R)0, (R)0};
 #pragma unroll
         for (int s = 0; s < 2; s++) {
             const bool conv = rr[s] < thr[s];
             fin[s] = conv || it >= maxit || !(rr[s] <= O::huge());
+            R* const xs = a.x[s];
+            R* const ps = a.p[s];
             if (fin[s]) {
                 iters[s] = conv ? it - 1 : it;
                 if (!conv) abs_old[s] = rz[s];
-            } else {
-                beta[s] = rz[s] / abs_old[s];
-                abs_old[s] = rz[s];
-            }
-        }
-        // ---------------- phase C (both systems per row block, ascending): x += alpha p; p = D^-1 r + beta p ----------------
-        for (int64_t i = gtid; i < nvec; i += gthreads) {
+                for (int64_t i = gtid; i < nvec; i += gthreads) {  // the deferred x += alpha p of the last iteration
+                    R xv[N], pv[N];
+                    if (first) {
 #pragma unroll
-            for (int s = 0; s < 2; s++) {
-                R* const xs = a.x[s];
-                R* const ps = a.p[s];
-                R xv[N], pv[N];
-                if (first) {
-#pragma unroll
-                    for (int q = 0; q < N; q++) xv[q] = (R)0;
-                } else {
-                    vload_cs<R>(xs + i * N, xv);
-                }
-                vload<R>(ps + i * N, pv);
-                if (fin[s]) {  // the deferred x += alpha p of the last iteration
+                        for (int q = 0; q < N; q++) xv[q] = (R)0;
+                    } else {
+                        vload_cs<R>(xs + i * N, xv);
+                    }
+                    vload<R>(ps + i * N, pv);
 #pragma unroll
                     for (int q = 0; q < N; q++) xv[q] = O::add(xv[q], O::mul(alpha[s], pv[q]));
                     vstore_cs<R>(xs + i * N, xv);
-                } else {
-                    R rv[N], dv[N];
-                    vload<R>(a.r[s] + i * N, rv);
-                    vload<R>(a.dinv[s] + i * N, dv);
+                }
+                if (blockIdx.x == 0)
+                    for (int64_t i = nvec * N + threadIdx.x; i < n; i += blockDim.x) xs[i] = O::add(first ? (R)0 : xs[i], O::mul(alpha[s], ps[i]));
+            } else {
+                const R beta = rz[s] / abs_old[s];
+                abs_old[s] = rz[s];
+                const R* const rs = a.r[s];
+                const R* const ds = a.dinv[s];
+                for (int64_t j = gtid; j < nvec; j += gthreads) {
+                    const int64_t i = a.zigzag ? nvec - 1 - j : j;
+                    R xv[N], rv[N], pv[N], dv[N];
+                    if (first) {
+#pragma unroll
+                        for (int q = 0; q < N; q++) xv[q] = (R)0;
+                    } else {
+                        vload_cs<R>(xs + i * N, xv);
+                    }
+                    vload<R>(rs + i * N, rv);
+                    vload<R>(ps + i * N, pv);
+                    vload<R>(ds + i * N, dv);
 #pragma unroll
                     for (int q = 0; q < N; q++) {
                         xv[q] = O::add(xv[q], O::mul(alpha[s], pv[q]));
-                        pv[q] = O::add(O::mul(dv[q], rv[q]), O::mul(beta[s], pv[q]));
+                        pv[q] = O::add(O::mul(dv[q], rv[q]), O::mul(beta, pv[q]));
                     }
                     vstore_cs<R>(xs + i * N, xv);
                     vstore<R>(ps + i * N, pv);
@@ -356,25 +361,17 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a, Com
                         pushed = true;
                     }
                 }
-            }
-        }
-        if (blockIdx.x == 0) {
-#pragma unroll
-            for (int s = 0; s < 2; s++) {
-                R* const xs = a.x[s];
-                R* const ps = a.p[s];
-                for (int64_t i = nvec * N + threadIdx.x; i < n; i += blockDim.x) {
-                    const R pi = ps[i];
-                    xs[i] = O::add(first ? (R)0 : xs[i], O::mul(alpha[s], pi));
-                    if (!fin[s]) {
-                        const R pn = O::add(O::mul(a.dinv[s][i], a.r[s][i]), O::mul(beta[s], pi));
+                if (blockIdx.x == 0)
+                    for (int64_t i = nvec * N + threadIdx.x; i < n; i += blockDim.x) {
+                        const R pi = ps[i];
+                        xs[i] = O::add(first ? (R)0 : xs[i], O::mul(alpha[s], pi));
+                        const R pn = O::add(O::mul(ds[i], rs[i]), O::mul(beta, pi));
                         ps[i] = pn;
                         if (cm.world > 1) {
                             push_row(s, i, pn);
                             pushed = true;
                         }
                     }
-                }
             }
         }
         DUAL_STAMP(6)

@@ -44,7 +44,8 @@ struct PcgArgs {
                        // from the RHS kernel's published sums (mailbox all-reduce number ar_seq); 0: CgState is already set
     R tol;
     int maxit;
-    int zigzag;        // phase B walks the rows descending (L2 reuse across the phase boundaries); FEAB_ZIGZAG=0 switches it off
+    int zigzag;        // phase C walks the rows DESCENDING: the boundary rows (last), whose new p goes to the neighbours over NVLink,
+                       // come first, so the remote stores are long acknowledged when the CTA fences before the grid sync; FEAB_ZIGZAG=0: ascending
     unsigned long long* prof; // optional (FEAB_PCG_PROF=1): ns spent by CTA 0 in [A, sync1 (barrier + all-reduce of p.Ap), -, B, sync2, -, C, sync3, -], iterations
 };
 
@@ -319,12 +320,9 @@ __global__ void __launch_bounds__(ROWS, MINB) pcg_persistent(PcgArgs<R> a, Comm 
         // ---------------- phase B: r -= alpha y, |r|^2, r.z  (ConjugateGradient.h:67-76) --------------------------
         // x += alpha p is deferred to phase C, which reads p anyway (one vector read less per iteration; same
         // operations on the same operands, so the same bits).
-        // Rows are walked DESCENDING: the SpMV wrote y ascending, so its last rows are still in L2 here, and phase C
-        // (ascending) starts on the rows this phase touched last.
         const R alpha = abs_old / pap[0];
         R prr = (R)0, prz = (R)0;
-        for (int64_t j = gtid; j < nvec; j += gthreads) {
-            const int64_t i = a.zigzag ? nvec - 1 - j : j;
+        for (int64_t i = gtid; i < nvec; i += gthreads) {
             R rv[N], yv[N], dv[N];
             vload<R>(rs + i * N, rv);
             vload<R>(a.y + i * N, yv);
@@ -386,7 +384,8 @@ __global__ void __launch_bounds__(ROWS, MINB) pcg_persistent(PcgArgs<R> a, Comm 
         const R beta = rz / abs_old;
         abs_old = rz;
         bool pushed = false;
-        for (int64_t i = gtid; i < nvec; i += gthreads) {
+        for (int64_t j = gtid; j < nvec; j += gthreads) {
+            const int64_t i = a.zigzag ? nvec - 1 - j : j;
             R xv[N], rv[N], pv[N], dv[N];
             if (first) {
 #pragma unroll

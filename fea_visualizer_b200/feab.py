@@ -23,12 +23,12 @@ SYNC_NONE, SYNC_FULL, SYNC_ROOT = 0, 1, 2
 
 # every symbol include/feab.h declares (checked by tests/test_abi.py without a GPU)
 ABI_SYMBOLS = [
-    "feab_create", "feab_destroy", "feab_last_error", "feab_set_mesh", "feab_set_boundary_condition", "feab_assemble",
+    "feab_create", "feab_destroy", "feab_last_error", "feab_set_mesh", "feab_set_mesh_ex", "feab_set_boundary_condition", "feab_assemble",
     "feab_get_counts", "feab_get_idx_map", "feab_get_csr", "feab_set_equation", "feab_set_params", "feab_get_params",
     "feab_set_solver_options", "feab_get_solver_options", "feab_clear", "feab_set_values", "feab_get_values", "feab_brush",
     "feab_step", "feab_unstable", "feab_last_stats", "feab_get_state", "feab_set_state", "feab_time_kernel",
     "feab_device_info", "feab_mg_config", "feab_mg_set_partition", "feab_partition_rcb", "feab_mg_export", "feab_mg_connect",
-    "feab_mg_get_layout", "feab_mg_get_maps", "feab_mg_group_step", "feab_pcg_profile",
+    "feab_mg_get_layout", "feab_mg_get_maps", "feab_mg_get_partition", "feab_mg_group_step", "feab_pcg_profile",
 ]
 
 
@@ -277,6 +277,11 @@ class Feab:
         a, b, c, d = C.c_int64(), C.c_int64(), C.c_int64(), C.c_int64()
         self._ck(self.lib.feab_mg_get_layout(self.h, C.byref(a), C.byref(b), C.byref(c), C.byref(d)))
         return {"n_own": a.value, "n_interior": b.value, "n_ghost": c.value, "n_cols": d.value}
+
+    def mg_partition(self):
+        out = np.empty(self.V, dtype=np.int32)
+        self._ck(self.lib.feab_mg_get_partition(self.h, C.c_void_p(out.ctypes.data)))
+        return out
 
     def mg_maps(self):
         lay = self.mg_layout()

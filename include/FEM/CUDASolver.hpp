@@ -138,11 +138,10 @@ class CUDASolver : public Solver {
         if (msig != mesh_sig_) {
             std::vector<uint8_t> onb(s.on_boundary.size());
             for (size_t i = 0; i < onb.size(); i++) onb[i] = s.on_boundary[i] ? 1 : 0;
-            check(feab_set_boundary_condition(h_, (int)c.boundary_condition), "feab_set_boundary_condition");
-            check(feab_set_mesh(h_, (int64_t)s.vertices.size(), reinterpret_cast<const float*>(s.vertices.data()), (int64_t)s.triangles.size(),
-                                reinterpret_cast<const uint32_t*>(s.triangles.data()), onb.data()),
-                  "feab_set_mesh");
-            check(feab_assemble(h_, v3), "feab_assemble");
+            // boundary condition and velocity travel with the mesh: one pattern build, one assembly per surface load
+            check(feab_set_mesh_ex(h_, (int64_t)s.vertices.size(), reinterpret_cast<const float*>(s.vertices.data()), (int64_t)s.triangles.size(),
+                                   reinterpret_cast<const uint32_t*>(s.triangles.data()), onb.data(), (int)c.boundary_condition, v3),
+                  "feab_set_mesh_ex");
             mesh_sig_ = msig;
             asm_sig_ = asig;
             publish_counts();

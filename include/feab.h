@@ -105,6 +105,11 @@ const char* feab_last_error(const FeabHandle* h);
  * on_boundary V bytes.  Builds idx_map, the CSR pattern, the scatter map, and assembles M, K, Adv. */
 int feab_set_mesh(FeabHandle* h, int64_t num_vertices, const float* xyz, int64_t num_triangles, const uint32_t* tri,
                   const uint8_t* on_boundary);
+/* The same with the context's boundary condition and advection velocity (NULL = keep) taken in the same call: a surface load
+ * (src/Application.cpp:593-596, :620-623: init_from_surface with whatever fem_ctx->boundary_condition and velocity hold)
+ * costs ONE pattern build and ONE assembly instead of one per setter. */
+int feab_set_mesh_ex(FeabHandle* h, int64_t num_vertices, const float* xyz, int64_t num_triangles, const uint32_t* tri,
+                     const uint8_t* on_boundary, int bc, const float* velocity3);
 /* fem_ctx->boundary_condition = bc; update_boundary_conditions() (src/FEM/FEMContext.cpp:224-240).
  * Does NOT touch solver state; callers follow with feab_clear like Application does (src/Application.cpp:313-316). */
 int feab_set_boundary_condition(FeabHandle* h, int bc);
@@ -181,6 +186,9 @@ int feab_mg_get_layout(FeabHandle* h, int64_t* n_own, int64_t* n_interior, int64
 /* row_node[n_own]: mesh node of every local row; col_unknown[n_cols]: global unknown id (idx_map numbering) of every
  * local column, -1 for padding.  With these, feab_get_csr / feab_get_state of a rank can be placed in the global system. */
 int feab_mg_get_maps(FeabHandle* h, int32_t* row_node, int32_t* col_unknown);
+/* part[] actually in use (length num_vertices): the array given to feab_mg_set_partition, or the default recursive coordinate
+ * bisection, which feab_set_mesh computes on the device and which equals feab_partition_rcb (host) element for element. */
+int feab_mg_get_partition(FeabHandle* h, int32_t* part_out);
 /* Test driver: advances `count` handles that live in THIS process on ONE device ("virtual ranks") in lock-step,
  * phase by phase on one stream, so that no kernel ever waits for a kernel that has not been launched yet.  Exercises
  * the partitioned data path (numbering, halo pushes, mailbox all-reduce) without `count` GPUs. */

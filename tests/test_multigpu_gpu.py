@@ -311,3 +311,36 @@ def test_threaded_ranks_bicgstab_partitioned(name, bc, world):
     run_steps(G, V, 2, 4, per_step=check)
     assert worst[0] <= 1e-10, worst      # vs one GPU: summation order of the dot products (BiCGSTAB amplifies it more than CG)
     assert worst[1] <= 1e-8, worst       # vs the fp64 oracle
+
+
+@pytest.mark.parametrize("name", ["ico12", "disk14", "grid", "ico40r", "fan"])
+def test_device_rcb_equals_host_rcb(name):
+    """The default partition is computed on the device (csrc/partition.cuh: bounding box, radix select of the split coordinate,
+    ties by vertex index) and must be the array feab_partition_rcb (host, std::nth_element) returns, element for element, for
+    every world size -- grids and disks have thousands of equal coordinates (the tie path), the icospheres have +-0."""
+    if name == "ico40r":
+        xyz, tri = meshes.icosphere(40, radius=40 / 32.0)
+    elif name == "fan":
+        xyz, tri = meshes.fan_refined(*meshes.grid(40, 30, 1.25, 0.9375))
+    else:
+        xyz, tri, _ = mesh(name)
+    ob = meshes.boundary_flags(len(xyz), tri)
+    for world in (2, 3, 4, 5, 7, 8):
+        h = feab.Feab(real=64)
+        h.mg_config(world - 1, world)
+        h.set_mesh(xyz, tri, ob)
+        got = h.mg_partition()
+        want = feab.partition_rcb(xyz, world)
+        assert (got == want).all(), (name, world, int((got != want).sum()))
+        h.close()
+
+
+def test_set_mesh_rejects_out_of_range_triangle_indices():
+    xyz, tri, ob = mesh("grid")
+    bad = tri.copy()
+    bad[3, 1] = len(xyz)
+    h = feab.Feab(real=64)
+    with pytest.raises(feab.FeabError):
+        h.set_mesh(xyz, bad, ob)
+    h.set_mesh(xyz, tri, ob)      # the handle is still usable
+    h.step(1)

@@ -127,8 +127,12 @@ def test_velocity_change_reassembles_and_bc_switch():
 @pytest.mark.parametrize("name", ["ico4", "grid", "disk", "ico8d"])
 @pytest.mark.parametrize("bc", [0, 1])
 @pytest.mark.parametrize("eq", [0, 1, 2, 3])
-def test_step_parity_fp64(name, bc, eq):
-    """Per-step relative L2 vs the fp64 oracle <= 1e-8 for every equation (adv-diff in reference-parity mode)."""
+@pytest.mark.parametrize("kernel", ["cluster", "grid"])
+def test_step_parity_fp64(name, bc, eq, kernel, monkeypatch):
+    """Per-step relative L2 vs the fp64 oracle <= 1e-8 for every equation (adv-diff in reference-parity mode), through both
+    persistent drivers: the one-cluster whole-step kernel that small meshes get by default (pcg_cluster.cuh) and, with
+    FEAB_CLUSTER=0, the grid-wide kernels every larger mesh runs (pcg_persistent / pcg_dual)."""
+    monkeypatch.setenv("FEAB_CLUSTER", "1" if kernel == "cluster" else "0")
     xyz, tri = cases()[name]
     ob = meshes.boundary_flags(len(xyz), tri)
     D = O.Oracle(xyz, tri, ob, bc, real=64)
@@ -228,6 +232,7 @@ def test_gray_scott_dual_solve_kernel(name, bc, monkeypatch):
     to the single-system kernel when the first one stops.  Same recurrences: per-step parity vs the fp64 oracle <= 1e-8, the
     iteration counts of both solves equal to the separate-solve path, fields equal to it to summation order, and
     run-to-run identical bits."""
+    monkeypatch.setenv("FEAB_CLUSTER", "0")   # small meshes would otherwise take the one-cluster kernel (pcg_cluster.cuh)
     xyz, tri = meshes.icosphere(24) if name == "ico24" else cases()[name]
     ob = meshes.boundary_flags(len(xyz), tri)
     V = len(xyz)
@@ -257,6 +262,7 @@ def test_gray_scott_dual_solve_kernel(name, bc, monkeypatch):
 
 
 def test_gray_scott_dual_solve_zero_rhs_and_fp32(monkeypatch):
+    monkeypatch.setenv("FEAB_CLUSTER", "0")
     monkeypatch.setenv("FEAB_DUAL", "1")
     xyz, tri = meshes.disk(7)
     ob = meshes.boundary_flags(len(xyz), tri)
@@ -448,12 +454,13 @@ def _fan_cases():
 @pytest.mark.parametrize("name,bc", [("fan_ico20", 0), ("fan_grid40x30", 0), ("fan_grid40x30", 1)])
 @pytest.mark.parametrize("eq", [0, 1, 2, 3])
 @pytest.mark.parametrize("loop", [feab.LOOP_PERSISTENT, feab.LOOP_GRAPH_WHILE])
-def test_rows_above_the_tile_staging_capacity(name, bc, eq, loop):
+def test_rows_above_the_tile_staging_capacity(name, bc, eq, loop, monkeypatch):
     """Fan-refined meshes (meshes.fan_refined): the base vertices come first and have 13 entries per row, so whole 256- and
     512-row tiles hold more than 8 entries per row and the tile kernels take their un-staged path (spmv_dot_tma, rhs_init_tma,
     pcg_persistent, pcg_dual read values / columns straight from global memory); the tile that straddles the base block and the
     centroid rows is staged with rows longer than 8 (the `len >= 8` tail).  All four equations, Gray-Scott through pcg_dual
     (persistent driver) and through the three-kernel WHILE graph.  Bar: 1e-8 relative L2 per step vs the fp64 oracle."""
+    monkeypatch.setenv("FEAB_CLUSTER", "0")   # the tile kernels are the subject here
     xyz, tri = _fan_cases()[name]
     V = len(xyz)
     ob = meshes.boundary_flags(V, tri)
@@ -516,3 +523,88 @@ def test_bicgstab_mode_against_eigens_own_bicgstab(name, bc, loop):
         assert err <= 2.3e-16 and rel_l2(got, x) <= 1e-10, (step, err, rel_l2(got, x))   # info() compares error() with the ABSOLUTE tolerance: not used
         assert abs(st["iterations"][0] - it) <= 4, (st["iterations"], it)   # BiCGSTAB's residual is not monotone: the crossing of eps moves by a few trips with the summation order
         assert np.linalg.norm(b - A @ got) / np.linalg.norm(b) <= 1e-12
+
+
+# ---------------------------------------------------------------------------------------------- one-cluster whole-step kernel
+@pytest.mark.parametrize("name,bc", [("bundled", 0), ("fan_ico20", 0), ("fan_grid40x30", 0), ("fan_grid40x30", 1), ("ico60d", 0), ("tiny", 1)])
+def test_cluster_kernel_steps_in_one_launch(name, bc, monkeypatch):
+    """pcg_cluster.cuh: meshes up to 65 536 rows run whole time steps -- K of them per launch -- inside one thread-block cluster.
+    All four equations on the reference's bundled icosphere (C1), rows of 13 entries, the 36 002-vertex bunny surrogate (C2,
+    the largest rows-per-CTA block) and a mesh with fewer rows than one CTA has threads: after 3 single steps and one 4-step
+    device-resident call the fields are within 1e-8 of the fp64 oracle stepping one by one, the iteration counts match, the
+    grid-wide kernels (FEAB_CLUSTER=0) agree to summation order, and two runs give the same bits."""
+    if name == "bundled":
+        g = load_golden("ref_assets.npz")
+        xyz, tri = g["icosphere/xyz"], g["icosphere/tri"]
+    elif name == "ico60d":
+        xyz, tri = meshes.icosphere(60, displace=True, radius=60 / 32.0)
+    elif name == "tiny":
+        xyz, tri = meshes.grid(5, 4)
+    else:
+        xyz, tri = _fan_cases()[name]
+    V = len(xyz)
+    ob = meshes.boundary_flags(V, tri)
+    seeds = meshes.seed_nodes(V)
+    v0 = np.zeros(V, np.float32)
+    v0[seeds] = 1.0
+    D = O.Oracle(xyz, tri, ob, bc, real=64)
+    monkeypatch.setenv("FEAB_CLUSTER", "1")
+    C1 = make(64, xyz, tri, ob, bc, assembly=feab.ASSEMBLY_ORDERED)
+    C2 = make(64, xyz, tri, ob, bc, assembly=feab.ASSEMBLY_ORDERED)
+    monkeypatch.setenv("FEAB_CLUSTER", "0")
+    G = make(64, xyz, tri, ob, bc, assembly=feab.ASSEMBLY_ORDERED)
+    for eq in (0, 1, 2, 3):
+        for X in (D, C1, C2, G):
+            X.clear()
+            X.set_equation(eq)
+            X.set_values(v0)
+        for s in range(3):
+            for X in (D, C1, C2, G):
+                X.step(1)
+            e = [rel_l2(C1.get_state(0), D.get_state(0)), rel_l2(C1.get_state(1), D.get_state(1)), rel_l2(C1.get_values(), D.get_values())]
+            assert max(e) <= FP64_STEP_TOL, (eq, s, e)
+            oit = D.last_stats()[0]
+            git = C1.stats()["iterations"]
+            assert abs(git[0] - int(oit[0])) <= 3 and abs(git[1] - int(oit[1])) <= 3, (eq, s, git, oit)
+            assert rel_l2(C1.get_state(0), G.get_state(0)) <= 1e-11 and rel_l2(C1.get_state(1), G.get_state(1)) <= 1e-11, (eq, s)
+        launches = C1.stats()["kernel_launches"]
+        for X in (C1, C2, G):
+            X.step(4)                         # one launch for the cluster handles
+        assert C1.stats()["kernel_launches"] - launches == 1
+        assert G.stats()["kernel_launches"] > launches
+        D.step(4)
+        e = [rel_l2(C1.get_state(0), D.get_state(0)), rel_l2(C1.get_state(1), D.get_state(1))]
+        assert max(e) <= 4 * FP64_STEP_TOL, (eq, e)
+        assert rel_l2(C1.get_values(), D.get_values()) <= 1e-6          # float32 values
+        assert (C1.get_state(0) == C2.get_state(0)).all() and (C1.get_state(1) == C2.get_state(1)).all()     # bit-reproducible
+        assert C1.unstable() == D.unstable()
+        assert C1.stats()["shared_iterations"] == 0
+
+
+def test_cluster_kernel_instability_zero_rhs_and_dirichlet_zeros(monkeypatch):
+    """The epilogue semantics of the cluster kernel: the instability flag belongs to the LAST step of a multi-step launch
+    (signed check, src/FEM/CPUSolver.cpp:41-48), a zero right-hand side returns x = 0 with 0 iterations
+    (ConjugateGradient.h:45-49), Dirichlet nodes are forced to 0 on exit (src/FEM/CPUSolver.cpp:28-36)."""
+    monkeypatch.setenv("FEAB_CLUSTER", "1")
+    xyz, tri = meshes.disk(10)
+    V = len(xyz)
+    ob = meshes.boundary_flags(V, tri)
+    F = make(64, xyz, tri, ob, 0)
+    D = O.Oracle(xyz, tri, ob, 0, real=64)
+    for X in (F, D):
+        X.clear()
+        X.set_equation(0)
+        X.set_values(np.zeros(V, np.float32))
+        X.step(2)
+    assert F.stats()["iterations"][0] == 0 and not F.get_values().any()
+    big = np.full(V, 5e4, np.float32)
+    for X in (F, D):
+        X.set_values(big)
+        X.step(1)
+    assert F.unstable() and D.unstable()
+    assert (F.get_values()[ob != 0] == 0).all()
+    for X in (F, D):
+        X.set_values(np.full(V, -5e4, np.float32))
+        X.step(3)
+    assert not F.unstable() and not D.unstable()
+    assert rel_l2(F.get_state(0), D.get_state(0)) <= 4 * FP64_STEP_TOL
