@@ -135,6 +135,7 @@ class SolverT final : public SolverBase {
         CK(cudaEventCreate(&ev0_));
         CK(cudaEventCreate(&ev1_));
         CK(cudaMallocHost(&h_flag_, 64));
+        std::memset(h_flag_, 0, 64);  // [8]: pcg_cluster's inter-cluster barrier gave up (written by the device)
         sms_ = prop_.multiProcessorCount;
         // opt in to > 48 KB dynamic shared memory for the tile kernels
         const int sm1 = kTileCap * (int)sizeof(R), sm2 = 2 * kTileCap * (int)sizeof(R);
@@ -156,6 +157,8 @@ class SolverT final : public SolverBase {
         opt_.assembly = FEAB_ASSEMBLY_SCATTER;
         CK(cudaMalloc(&d_unstable_, sizeof(int)));
         CK(cudaMemset(d_unstable_, 0, sizeof(int)));
+        CK(cudaMalloc(&d_xbar_, sizeof(unsigned long long)));
+        CK(cudaMemset(d_xbar_, 0, sizeof(unsigned long long)));
         CK(cudaMalloc(&d_st_, 2 * sizeof(CgState<R>)));
         CK(cudaMemset(d_st_, 0, 2 * sizeof(CgState<R>)));
         CK(cudaMalloc(&d_bst_, sizeof(BicgState<R>)));
@@ -209,6 +212,7 @@ class SolverT final : public SolverBase {
         if (dual_max_grid_ > 0) d_dpart_.alloc((size_t)6 * dual_max_grid_);
         if (const char* v = getenv("FEAB_DUAL")) dual_ = atoi(v) != 0;
         if (const char* v = getenv("FEAB_ZIGZAG")) zigzag_ = atoi(v) != 0 ? 1 : 0;
+        if (const char* v = getenv("FEAB_COOP")) coop_launch_ = atoi(v) != 0;
         // non-symmetric mode: the whole BiCGSTAB solve as one cooperative kernel (bicg_persistent.cuh), same tile geometry
         CK(cudaFuncSetAttribute(bicg_persistent<R, kPcgRows, kPcgCpr, kPcgStages, kPcgMinB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)PCfg::kSmemBytes));
@@ -238,8 +242,12 @@ class SolverT final : public SolverBase {
                 cfg.attrs = at;
                 cfg.numAttrs = 1;
                 int nclusters = 0;
-                if (cudaOccupancyMaxActiveClusters(&nclusters, pcg_cluster<R, 1024>, &cfg) == cudaSuccess && nclusters >= 1) cluster_ctas_ = cs;
+                if (cudaOccupancyMaxActiveClusters(&nclusters, pcg_cluster<R, 1024>, &cfg) == cudaSuccess && nclusters >= 1) {
+                    cluster_ctas_ = cs;
+                    cluster_pair_ = nclusters >= 2;  // Gray-Scott: one cluster per system, side by side (they meet at a spin barrier: both must be resident)
+                }
             }
+            if (const char* v = getenv("FEAB_CLUSTER_PAIR")) cluster_pair_ = cluster_pair_ && atoi(v) != 0;
             cudaGetLastError();
             if (const char* v = getenv("FEAB_CLUSTER"))
                 if (atoi(v) == 0) cluster_ctas_ = 0;
@@ -358,6 +366,7 @@ class SolverT final : public SolverBase {
         cudaDeviceSynchronize();
         drop_graphs();
         if (d_unstable_) cudaFree(d_unstable_);
+        if (d_xbar_) cudaFree(d_xbar_);
         if (d_st_) cudaFree(d_st_);
         if (d_bst_) cudaFree(d_bst_);
         if (d_loc_) cudaFree(d_loc_);
@@ -1135,6 +1144,13 @@ class SolverT final : public SolverBase {
         return eq_ == FEAB_EQ_REACTION_DIFFUSION ? 2 : 1;
     }
 
+    // Launch of a persistent kernel whose CTAs sync with each other: the grid never exceeds what the device holds at once
+    // (occupancy x SMs, computed at creation).  A cooperative launch makes the driver check exactly that; FEAB_COOP=0 uses a
+    // plain launch of the same grid (an experiment switch: the co-residency argument is the same, the check is skipped).
+    cudaError_t launch_resident(const void* f, dim3 grid, dim3 block, void** args, size_t smem, cudaStream_t s) {
+        return coop_launch_ ? cudaLaunchCooperativeKernel(f, grid, block, args, smem, s) : cudaLaunchKernel(f, grid, block, args, smem, s);
+    }
+
     void launch_iteration(cudaStream_t s, int slot, const R* A, const R* dinv, R* x, cudaGraphConditionalHandle cond, int use_cond) {
         ph_spmv(s, slot, A);
         ph_update(s, slot, dinv, x);
@@ -1175,7 +1191,7 @@ class SolverT final : public SolverBase {
         using DCfg = DualCfg<R, kDualRows, kPcgCpr, kPcgStages>;
         void* kargs[] = {(void*)&da, (void*)&cm_, (void*)&hp_};
         if (time_solves_) CK(cudaEventRecord(ev_solve_[0], stream_));
-        CK(cudaLaunchCooperativeKernel((const void*)pcg_dual<R, kDualRows, kPcgCpr, kPcgStages, kPcgMinB>, dim3(grid), dim3(2 * kDualRows), kargs,
+        CK(launch_resident((const void*)pcg_dual<R, kDualRows, kPcgCpr, kPcgStages, kPcgMinB>, dim3(grid), dim3(2 * kDualRows), kargs,
                                        DCfg::kSmemBytes, stream_));
         launches_ += 1;
         launch_pcg_persistent(-1, 0, A, dinv, x);
@@ -1210,7 +1226,7 @@ class SolverT final : public SolverBase {
         const int grid = std::min(pcg_max_grid_, pa.num_tiles);
         using PCfg = TmaCfg<R, kPcgRows, kPcgCpr, kPcgStages>;
         void* kargs[] = {(void*)&pa, (void*)&cm_, (void*)&hp_};
-        CK(cudaLaunchCooperativeKernel((const void*)pcg_persistent<R, kPcgRows, kPcgCpr, kPcgStages, kPcgMinB>, dim3(grid), dim3(kPcgRows), kargs,
+        CK(launch_resident((const void*)pcg_persistent<R, kPcgRows, kPcgCpr, kPcgStages, kPcgMinB>, dim3(grid), dim3(kPcgRows), kargs,
                                        PCfg::kSmemBytes, stream_));
         launches_ += 1;
     }
@@ -1246,7 +1262,7 @@ class SolverT final : public SolverBase {
         using PCfg = TmaCfg<R, kPcgRows, kPcgCpr, kPcgStages>;
         void* kargs[] = {(void*)&ba, (void*)&cm_, (void*)&hp_};
         if (time_solves_) CK(cudaEventRecord(ev_solve_[0], stream_));
-        CK(cudaLaunchCooperativeKernel((const void*)bicg_persistent<R, kPcgRows, kPcgCpr, kPcgStages, kPcgMinB>, dim3(grid), dim3(kPcgRows), kargs,
+        CK(launch_resident((const void*)bicg_persistent<R, kPcgRows, kPcgCpr, kPcgStages, kPcgMinB>, dim3(grid), dim3(kPcgRows), kargs,
                                        PCfg::kSmemBytes, stream_));
         if (time_solves_) CK(cudaEventRecord(ev_solve_[1], stream_));
         launches_ += 1;
@@ -1298,7 +1314,15 @@ class SolverT final : public SolverBase {
         }
         ca.u = d_u_.p;
         ca.v = d_v_.p;
-        ca.p = d_p_[0].p;
+        ca.p[0] = d_p_[0].p;
+        ca.p[1] = d_p_[1].p;
+        const bool pair = cluster_pair_ && eq_ == FEAB_EQ_REACTION_DIFFUSION;
+        ca.pair = pair ? 1 : 0;
+        ca.xbar = d_xbar_;
+        ca.xbar_base = xbar_count_;
+        if (pair) xbar_count_ += 4ull * (unsigned long long)nsteps;  // two meetings per step, two arrivals per meeting
+        ca.loc = cm_.loc;
+        ca.xerr = h_flag_ + 8;
         ca.values = d_values_.p;
         ca.node_of = node_of_col_p_;
         ca.dir_nodes = d_dir_nodes_.p;
@@ -1319,8 +1343,9 @@ class SolverT final : public SolverBase {
         step_stamp_ += nsteps;
         last_stamp_ = step_stamp_;
         cudaLaunchConfig_t cfg = {};
-        cfg.gridDim = dim3(C);
-        cfg.blockDim = dim3(cluster_threads_);
+        const int threads = cluster_threads_;
+        cfg.gridDim = dim3(pair ? 2 * C : C);
+        cfg.blockDim = dim3(threads);
         cfg.dynamicSmemBytes = base + (size_t)val_cap * sizeof(R) + (size_t)col_cap * sizeof(int);
         cfg.stream = stream_;
         cudaLaunchAttribute at[1];
@@ -1331,7 +1356,7 @@ class SolverT final : public SolverBase {
         cfg.attrs = at;
         cfg.numAttrs = 1;
         CK(cudaEventRecord(ev_solve_[0], stream_));
-        if (cluster_threads_ == 512)
+        if (threads == 512)
             CK(cudaLaunchKernelEx(&cfg, pcg_cluster<R, 512>, ca));
         else
             CK(cudaLaunchKernelEx(&cfg, pcg_cluster<R, 1024>, ca));
@@ -1592,6 +1617,13 @@ class SolverT final : public SolverBase {
             time_solves_ = false;
         }
         check_comm_error();
+        if (cluster_steps_last_ > 0 && h_flag_[8]) {  // pair mode of pcg_cluster: the other cluster never arrived
+            const int who = h_flag_[8];
+            h_flag_[8] = 0;
+            CK(cudaMemset(&d_loc_->error, 0, sizeof(int)));
+            throw Err{FEAB_ECOMM, "step: cluster " + std::to_string(who - 1) + " of the small-mesh kernel timed out waiting for the other cluster; "
+                                  "the fields of this call are not valid (FEAB_CLUSTER_PAIR=0 runs the two solves in one cluster)"};
+        }
     }
 
     void read_states(CgState<R>* st2, BicgState<R>* bst) {
@@ -1725,7 +1757,7 @@ class SolverT final : public SolverBase {
         CK(cudaSetDevice(device_));
         unsigned long long h[16];
         CK(cudaMemcpy(h, d_prof_, sizeof(h), cudaMemcpyDeviceToHost));
-        for (int i = 0; i < 16; i++) out16[i] = (double)h[i];
+        for (int i = 0; i < 10; i++) out16[i] = (double)h[i];   // [10, 16) are the step-phase times above
         if (reset) CK(cudaMemset(d_prof_, 0, sizeof(h)));
     }
 
@@ -1945,10 +1977,14 @@ class SolverT final : public SolverBase {
     int bicg_max_grid_ = 0;
     int cluster_ctas_ = 0;      // largest cluster size pcg_cluster can be launched with (0: not available / switched off)
     int cluster_steps_last_ = 0;
-    int cluster_threads_ = 512;   // 16 warps per CTA and 128 registers per thread measured faster than 1024 x 64 (FEAB_CLUSTER_THREADS=1024)
+    bool cluster_pair_ = false;  // two clusters of that size can be resident together (FEAB_CLUSTER_PAIR=0: never use the second one)
+    unsigned long long* d_xbar_ = nullptr;  // arrivals at pcg_cluster's inter-cluster barriers
+    unsigned long long xbar_count_ = 0;     // ... and how many the launches so far account for
+    int cluster_threads_ = 512;   // 16 warps per CTA and 128 registers per thread measured faster than 768 x 80 and 1024 x 64 (FEAB_CLUSTER_THREADS=1024)
     int64_t cluster_ent_key_ = -1;
     int cluster_ent_max_ = 0;
     int grid_cap_ = INT32_MAX;
+    bool coop_launch_ = true;  // FEAB_COOP=0: plain launches of the persistent kernels (launch_resident)
     int zigzag_ = 1;     // FEAB_ZIGZAG=0: phase C of the persistent kernels walks the rows ascending (boundary rows and their NVLink pushes last)
     bool dual_ = true;   // FEAB_DUAL=0 runs the two Gray-Scott solves one after the other
     bool dual_last_ = false;

@@ -532,7 +532,9 @@ def test_cluster_kernel_steps_in_one_launch(name, bc, monkeypatch):
     All four equations on the reference's bundled icosphere (C1), rows of 13 entries, the 36 002-vertex bunny surrogate (C2,
     the largest rows-per-CTA block) and a mesh with fewer rows than one CTA has threads: after 3 single steps and one 4-step
     device-resident call the fields are within 1e-8 of the fp64 oracle stepping one by one, the iteration counts match, the
-    grid-wide kernels (FEAB_CLUSTER=0) agree to summation order, and two runs give the same bits."""
+    grid-wide kernels (FEAB_CLUSTER=0) agree to summation order, and two runs give the same bits.  Gray-Scott runs its two
+    solves side by side on two clusters when the device can hold both (ClusterArgs::pair); FEAB_CLUSTER_PAIR=0 keeps them in
+    one cluster, one after the other -- the same arithmetic per system, so the same bits."""
     if name == "bundled":
         g = load_golden("ref_assets.npz")
         xyz, tri = g["icosphere/xyz"], g["icosphere/tri"]
@@ -551,15 +553,18 @@ def test_cluster_kernel_steps_in_one_launch(name, bc, monkeypatch):
     monkeypatch.setenv("FEAB_CLUSTER", "1")
     C1 = make(64, xyz, tri, ob, bc, assembly=feab.ASSEMBLY_ORDERED)
     C2 = make(64, xyz, tri, ob, bc, assembly=feab.ASSEMBLY_ORDERED)
+    monkeypatch.setenv("FEAB_CLUSTER_PAIR", "0")
+    C3 = make(64, xyz, tri, ob, bc, assembly=feab.ASSEMBLY_ORDERED)
+    monkeypatch.delenv("FEAB_CLUSTER_PAIR")
     monkeypatch.setenv("FEAB_CLUSTER", "0")
     G = make(64, xyz, tri, ob, bc, assembly=feab.ASSEMBLY_ORDERED)
     for eq in (0, 1, 2, 3):
-        for X in (D, C1, C2, G):
+        for X in (D, C1, C2, C3, G):
             X.clear()
             X.set_equation(eq)
             X.set_values(v0)
         for s in range(3):
-            for X in (D, C1, C2, G):
+            for X in (D, C1, C2, C3, G):
                 X.step(1)
             e = [rel_l2(C1.get_state(0), D.get_state(0)), rel_l2(C1.get_state(1), D.get_state(1)), rel_l2(C1.get_values(), D.get_values())]
             assert max(e) <= FP64_STEP_TOL, (eq, s, e)
@@ -568,7 +573,7 @@ def test_cluster_kernel_steps_in_one_launch(name, bc, monkeypatch):
             assert abs(git[0] - int(oit[0])) <= 3 and abs(git[1] - int(oit[1])) <= 3, (eq, s, git, oit)
             assert rel_l2(C1.get_state(0), G.get_state(0)) <= 1e-11 and rel_l2(C1.get_state(1), G.get_state(1)) <= 1e-11, (eq, s)
         launches = C1.stats()["kernel_launches"]
-        for X in (C1, C2, G):
+        for X in (C1, C2, C3, G):
             X.step(4)                         # one launch for the cluster handles
         assert C1.stats()["kernel_launches"] - launches == 1
         assert G.stats()["kernel_launches"] > launches
@@ -577,6 +582,8 @@ def test_cluster_kernel_steps_in_one_launch(name, bc, monkeypatch):
         assert max(e) <= 4 * FP64_STEP_TOL, (eq, e)
         assert rel_l2(C1.get_values(), D.get_values()) <= 1e-6          # float32 values
         assert (C1.get_state(0) == C2.get_state(0)).all() and (C1.get_state(1) == C2.get_state(1)).all()     # bit-reproducible
+        assert (C1.get_state(0) == C3.get_state(0)).all() and (C1.get_state(1) == C3.get_state(1)).all()     # one cluster or two
+        assert (C1.get_values() == C3.get_values()).all() and C1.stats()["iterations"] == C3.stats()["iterations"]
         assert C1.unstable() == D.unstable()
         assert C1.stats()["shared_iterations"] == 0
 
