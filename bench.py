@@ -459,6 +459,7 @@ def main():
     passes = st["spmv_passes"]
     launches = st["kernel_launches"] - launches0
     solve_ms = st.get("solve_ms", 0.0)       # persistent loop: device time of the last step's PCG kernel(s)
+    solve_kernel = F.last_solve_kernel()     # "pcg_dual + pcg_persistent" (lock-step), "pcg_pair" (staggered), ...
     prof = F.pcg_profile(reset=True)          # FEAB_PCG_PROF=1: where CTA 0 of the persistent kernel spent its time
     step_ms = {"value_leg_last_step": prof["step_ms"]} if any(prof["step_ms"].values()) else None   # FEAB_STEP_PROF=1
     if prof["iterations"]:
@@ -520,8 +521,7 @@ def main():
             # the dominant kernels of the timed region: the persistent PCG solves (pcg_dual for the lock-step passes, pcg_persistent
             # for the longer solve's tail; pcg_persistent alone with FEAB_DUAL=0), events on the solver stream around the last step's
             traffic, traffic_src = ncu_solve_traffic(n, dt_name, passes, st.get("shared_iterations", 0))
-            head = {"kernel": "persistent PCG solve kernels of one step (pcg_dual + pcg_persistent tail)" if shared else
-                    "persistent PCG solve kernels of one step (pcg_persistent x 2)",
+            head = {"kernel": "persistent PCG solve kernels of one step (" + (solve_kernel or "pcg_persistent x2") + ")",
                     "achieved": solve_bytes / solve_ms / 1e6, "algorithmic_bytes": solve_bytes, "ms": solve_ms,
                     "traffic": traffic, "traffic_source": traffic_src}
         else:
@@ -571,7 +571,7 @@ def main():
                 "config": {"workload": workload, "rows": n_all, "nnz": nnz_all, "max_row": max_row,
                            "parallelism": "single GPU" if world == 1 else f"rows partitioned x{world} (RCB), P2P halo + mailbox all-reduce over NVLink",
                            "tolerance": "eps of dtype (Eigen default)" if args.tol < 0 else args.tol,
-                           "pcg_iterations_last_step": its, "spmv_passes_last_step": passes, "loop": args.loop,
+                           "pcg_iterations_last_step": its, "spmv_passes_last_step": passes, "loop": args.loop, "solve_kernel": solve_kernel,
                            "l2_policy": "inputs larger than L2 (matrix + vectors >> 126 MB)", "setup_s": setup_s,
                            "timed_steps": f"steps {warm}..{warm + args.steps - 1} of the run, in both legs (state restored from a snapshot in between)"},
                 "us_per_pcg_iteration": (solve_ms * 1e3 / max(1, its[0] + its[1])) if solve_ms else None,

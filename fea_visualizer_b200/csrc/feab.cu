@@ -122,6 +122,7 @@ struct SolverBase {
     virtual int64_t ls_maxit() = 0;
     virtual void ls_finish_call(int nsteps) = 0;
     virtual int device() const = 0;
+    virtual const char* last_solve_kernel() const = 0;
 };
 
 template <typename R>
@@ -194,8 +195,9 @@ class SolverT final : public SolverBase {
             step_prof_ = atoi(v) != 0;
             for (int i = 0; i < 8; i++) CK(cudaEventCreate(&ev_ph_[i]));
         }
-        if (const char* v = getenv("FEAB_PCG_PROF")) {  // 1: stamps of pcg_persistent, 2: stamps of pcg_dual
-            prof_dual_ = atoi(v) == 2;
+        if (const char* v = getenv("FEAB_PCG_PROF")) {  // 1: stamps of pcg_persistent, 2: stamps of pcg_dual, 3: + every CTA's sync arrival times
+            prof_dual_ = atoi(v) >= 2;
+            prof_arrivals_ = atoi(v) == 3;
             CK(cudaMalloc(&d_prof_, 16 * sizeof(unsigned long long)));
             CK(cudaMemset(d_prof_, 0, 16 * sizeof(unsigned long long)));
         }
@@ -1187,6 +1189,12 @@ class SolverT final : public SolverBase {
         da.maxit = maxit();
         da.zigzag = zigzag_;
         da.prof = prof_dual_ ? d_prof_ : nullptr;
+        da.arrivals = nullptr;
+        if (prof_arrivals_) {
+            d_arrivals_.alloc((size_t)6 * std::max(dual_max_grid_, 1));
+            da.arrivals = d_arrivals_.p;
+            arrivals_grid_ = std::min(dual_max_grid_, da.num_tiles);
+        }
         const int grid = std::min(dual_max_grid_, da.num_tiles);
         using DCfg = DualCfg<R, kDualRows, kPcgCpr, kPcgStages>;
         void* kargs[] = {(void*)&da, (void*)&cm_, (void*)&hp_};
@@ -1363,6 +1371,7 @@ class SolverT final : public SolverBase {
         CK(cudaEventRecord(ev_solve_[1], stream_));
         launches_ += 1;
         cluster_steps_last_ = nsteps;
+        solve_kernel_ = "pcg_cluster";
         dual_last_ = false;
     }
 
@@ -1427,6 +1436,7 @@ class SolverT final : public SolverBase {
         ph_step_collect(stream_, capturing);
         if (!capturing) mark(2);
         if (use_bicgstab()) {
+            solve_kernel_ = persistent_solves(capturing) ? "bicg_persistent" : capturing ? "graph" : "host";
             if (persistent_solves(capturing))
                 launch_bicg_persistent();
             else
@@ -1437,6 +1447,8 @@ class SolverT final : public SolverBase {
             R* x[2];
             const int ns = solves(A, dinv, x);
             dual_last_ = ns == 2 && dual_applies(capturing);
+            solve_kernel_ = capturing ? "graph" : dual_last_ ? "pcg_dual + pcg_persistent"
+                            : opt_.loop_mode == FEAB_LOOP_PERSISTENT && !lockstep_ ? (ns == 2 ? "pcg_persistent x2" : "pcg_persistent") : "host";
             if (dual_last_)
                 enqueue_dual(A, dinv, x);
             else
@@ -1566,6 +1578,7 @@ class SolverT final : public SolverBase {
                 time_solves_ = !graph_mode && opt_.loop_mode == FEAB_LOOP_PERSISTENT && s == nsteps - 1;
                 mark_now_ = !graph_mode && s == nsteps - 1;
                 if (graph_mode) {
+                    solve_kernel_ = "graph";
                     CK(cudaGraphLaunch(graph_exec_, stream_));
                     graph_steps_++;
                 } else {
@@ -1749,8 +1762,29 @@ class SolverT final : public SolverBase {
         CK(cudaMemset(d_st_, 0, 2 * sizeof(CgState<R>)));
     }
 
+    // FEAB_PCG_PROF=3: when did the CTAs of pcg_dual enter and leave the three grid syncs of the last iteration?  (stderr)
+    void report_arrivals() {
+        if (!prof_arrivals_ || arrivals_grid_ <= 0) return;
+        const int G = arrivals_grid_;
+        std::vector<unsigned long long> h((size_t)6 * G);
+        CK(cudaMemcpy(h.data(), d_arrivals_.p, h.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+        static const char* names[3] = {"sync1 (after SpMV)", "sync2 (after update)", "sync3 (after direction)"};
+        for (int k = 0; k < 3; k++) {
+            std::vector<unsigned long long> in(h.begin() + (size_t)(2 * k) * G, h.begin() + (size_t)(2 * k + 1) * G);
+            std::vector<unsigned long long> out(h.begin() + (size_t)(2 * k + 1) * G, h.begin() + (size_t)(2 * k + 2) * G);
+            std::sort(in.begin(), in.end());
+            std::sort(out.begin(), out.end());
+            const double first = (double)in.front();
+            fprintf(stderr, "[feab] rank %d %s, %d CTAs: arrivals after the first one (us): p10 %.2f p50 %.2f p90 %.2f p99 %.2f last %.2f | first leaves %.2f, "
+                            "last leaves %.2f after the last arrival\n",
+                    rank_, names[k], G, (in[G / 10] - first) / 1e3, (in[G / 2] - first) / 1e3, (in[G * 9 / 10] - first) / 1e3, (in[G * 99 / 100] - first) / 1e3,
+                    (in.back() - first) / 1e3, ((double)out.front() - (double)in.back()) / 1e3, ((double)out.back() - (double)in.back()) / 1e3);
+        }
+    }
+
     void pcg_profile(double* out16, int reset) override {
         for (int i = 0; i < 16; i++) out16[i] = 0;
+        report_arrivals();
         if (step_prof_)
             for (int i = 0; i < 6; i++) out16[10 + i] = phase_ms_[i];
         if (!d_prof_) return;
@@ -1907,6 +1941,7 @@ class SolverT final : public SolverBase {
         check_comm_error();
     }
     int device() const override { return device_; }
+    const char* last_solve_kernel() const override { return solve_kernel_; }
 
     int sms() const { return sms_; }
     const cudaDeviceProp& prop() const { return prop_; }
@@ -1974,6 +2009,10 @@ class SolverT final : public SolverBase {
     // persistent whole-solve kernel
     int pcg_max_grid_ = 0;
     int dual_max_grid_ = 0;
+    const char* solve_kernel_ = "";      // feab_last_solve_kernel
+    bool prof_arrivals_ = false;         // FEAB_PCG_PROF=3
+    DevBuf<unsigned long long> d_arrivals_;
+    int arrivals_grid_ = 0;
     int bicg_max_grid_ = 0;
     int cluster_ctas_ = 0;      // largest cluster size pcg_cluster can be launched with (0: not available / switched off)
     int cluster_steps_last_ = 0;
@@ -2266,6 +2305,13 @@ int feab_mg_group_step(FeabHandle** hs, int count, int nsteps) {
     for (int i = 0; i < count; i++)
         if (!hs[i]) return FEAB_EINVAL;
     FEAB_TRY(hs[0], group_step_impl(hs, count, nsteps));
+}
+
+int feab_last_solve_kernel(FeabHandle* h, char* name64) {
+    if (!h || !name64) return FEAB_EINVAL;
+    std::strncpy(name64, h->impl->last_solve_kernel(), 63);
+    name64[63] = 0;
+    return FEAB_OK;
 }
 
 int feab_device_info(const FeabHandle* h, int* sm_count, int64_t* total_mem, char* name64) {

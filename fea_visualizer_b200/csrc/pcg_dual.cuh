@@ -38,6 +38,8 @@ struct PcgDualArgs {
     int maxit;
     int zigzag;  // see PcgArgs::zigzag
     unsigned long long* prof; // optional (FEAB_PCG_PROF=2): ns spent by CTA 0, same slots as PcgArgs::prof
+    unsigned long long* arrivals;  // optional (FEAB_PCG_PROF=3): globaltimer of every CTA when it enters / leaves each of the three grid
+                                   // syncs of the LAST iteration, [sync][enter, leave][gridDim.x] -- how much of a sync is waiting for the slowest CTA
 };
 
 template <typename R, int ROWS, int CPR, int STAGES>
@@ -148,6 +150,8 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a, Com
     R rr[2] = {(R)0, (R)0};
     const bool prof = a.prof != nullptr && blockIdx.x == 0 && threadIdx.x == 0;
     unsigned long long t_last = prof ? globaltimer_ns() : 0ull;
+#define DUAL_ARRIVAL(idx)                                                                                   \
+    if (a.arrivals != nullptr && threadIdx.x == 0) a.arrivals[(size_t)(idx)*gridDim.x + blockIdx.x] = globaltimer_ns();
 #define DUAL_STAMP(slot)                                   \
     if (prof) {                                            \
         const unsigned long long t_now = globaltimer_ns(); \
@@ -250,10 +254,12 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a, Com
         __syncthreads();
         prologue();
         DUAL_STAMP(0)
+        DUAL_ARRIVAL(0)
         if (!gsync_allreduce<R, 2, NWT>(cm, ar_seq, part, pap, red, s_v, s_ctl)) {
             failed = true;
             break;
         }
+        DUAL_ARRIVAL(1)
         DUAL_STAMP(1)
 
         // ---------------- phase B (both systems): r -= alpha y, |r|^2, r.z ----------------
@@ -294,10 +300,12 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a, Com
         }
         block_sum_vec<R, 4, NWT>(pb, red);
         DUAL_STAMP(3)
+        DUAL_ARRIVAL(2)
         if (!gsync_allreduce<R, 4, NWT>(cm, ar_seq, part + (size_t)2 * G, pb, red, s_v, s_ctl)) {
             failed = true;
             break;
         }
+        DUAL_ARRIVAL(3)
         DUAL_STAMP(4)
         R rz[2];
         rr[0] = pb[0];
@@ -378,10 +386,12 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a, Com
         if (fin[0] && fin[1]) break;
         if (cm.world == 1) {
             if (fin[0] || fin[1]) break;  // the kernel boundary is the barrier the survivor's next SpMV needs
+            DUAL_ARRIVAL(4)
             if (!gsync_barrier(cm, hp, bar_seq, 0ull, s_ctl)) {
                 failed = true;
                 break;
             }
+            DUAL_ARRIVAL(5)
             DUAL_STAMP(7)
         } else {
             // same hand-shake as pcg_persistent.cuh: pushers fence, grid sync, the last CTA to arrive raises the flags; one
@@ -389,15 +399,18 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a, Com
             // kernel waits for.
             if (__syncthreads_or(pushed ? 1 : 0)) __threadfence_system();
             halo_seq += 1;
+            DUAL_ARRIVAL(4)
             if (!gsync_barrier(cm, hp, bar_seq, halo_seq, s_ctl)) {
                 failed = true;
                 break;
             }
+            DUAL_ARRIVAL(5)
             DUAL_STAMP(7)
             if (fin[0] || fin[1]) break;
         }
     }
 #undef DUAL_STAMP
+#undef DUAL_ARRIVAL
     if (prof) a.prof[9] += (unsigned long long)(it - it0);
     // drain the prologue issued for an iteration that does not run here
     {

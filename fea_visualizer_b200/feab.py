@@ -29,6 +29,7 @@ ABI_SYMBOLS = [
     "feab_step", "feab_unstable", "feab_last_stats", "feab_get_state", "feab_set_state", "feab_time_kernel",
     "feab_device_info", "feab_mg_config", "feab_mg_set_partition", "feab_partition_rcb", "feab_mg_export", "feab_mg_connect",
     "feab_mg_get_layout", "feab_mg_get_maps", "feab_mg_get_partition", "feab_mg_group_step", "feab_pcg_profile",
+    "feab_last_solve_kernel",
 ]
 
 
@@ -249,6 +250,11 @@ class Feab:
         names = ["spmv", "sync1", "unused1", "update", "sync2", "unused2", "direction", "sync3", "unused3"]
         steps = ["upload", "gather_rhs", "solves", "epilogue", "broadcast", "download"]
         return {"ns": dict(zip(names, list(out)[:9])), "iterations": int(out[9]), "step_ms": dict(zip(steps, list(out)[10:16]))}
+
+    def last_solve_kernel(self):
+        name = C.create_string_buffer(64)
+        self._ck(self.lib.feab_last_solve_kernel(self.h, name))
+        return name.value.decode()
 
     def device_info(self):
         sm, mem = C.c_int(), C.c_int64()

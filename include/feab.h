@@ -199,7 +199,7 @@ int feab_mg_group_step(FeabHandle** handles, int count, int nsteps);
  * launch (CUDA events on the solver stream) and the algorithmic bytes one launch moves.
  * kernel: 0 = SpMV+dot, 1 = PCG vector update, 2 = PCG direction update, 3 = RHS build for the current equation */
 int feab_time_kernel(FeabHandle* h, int kernel, int reps, double* ms_per_launch, double* algorithmic_bytes);
-/* With FEAB_PCG_PROF=1 (pcg_persistent) or 2 (pcg_dual) in the environment at feab_create: nanoseconds CTA 0 of the
+/* With FEAB_PCG_PROF=1 (pcg_persistent, pcg_cluster) or 2 (pcg_dual; 3: plus the per-CTA sync arrival spread on stderr) in the environment at feab_create: nanoseconds CTA 0 of the
  * persistent PCG kernel spent in [0] SpMV phase, [1] grid sync merged with the all-reduce of p.Ap, [3] update phase,
  * [4] grid sync merged with the all-reduce of |r|^2, r.z, [6] direction phase (incl. halo stores), [7] grid sync that
  * raises the halo flags; [2], [5], [8] unused (they were separate all-reduce / push stages before the syncs were merged);
@@ -208,6 +208,10 @@ int feab_time_kernel(FeabHandle* h, int kernel, int reps, double* ms_per_launch,
  * stream): upload (+ root push), gather + RHS kernel, solve kernels, epilogue, value broadcast, download. */
 int feab_pcg_profile(FeabHandle* h, double* out16, int reset);
 int feab_device_info(const FeabHandle* h, int* sm_count, int64_t* total_mem_bytes, char* name64);
+/* Which kernel(s) ran the solve(s) of the LAST step (diagnostics; bench.py labels its roofline entry with it): "pcg_cluster",
+ * "pcg_dual + pcg_persistent" (Gray-Scott, lock-step), "pcg_persistent" / "pcg_persistent x2",
+ * "bicg_persistent", "graph" (WHILE-graph driver), "host" (host-batched driver), "" before the first step. */
+int feab_last_solve_kernel(FeabHandle* h, char* name64);
 
 #ifdef __cplusplus
 }
