@@ -37,7 +37,7 @@ struct BicgArgs {
     int num_tiles;
     int first_halo_tile;
     BicgState<R>* st;
-    R* part;          // 2 x gridDim.x
+    R* part;          // 4 x gridDim.x
     R tol;
     int maxit;
     unsigned long long* prof;  // optional: ns spent by CTA 0 in [S1+S2, all-reduces, -, P+S+X, barriers, ...], trips in [9]
@@ -61,6 +61,7 @@ __global__ void __launch_bounds__(ROWS, MINB) bicg_persistent(BicgArgs<R> a, Com
     unsigned long long ar_seq = *(volatile unsigned long long*)&cm.loc->ar_seq;
     unsigned long long halo_seq = *(volatile unsigned long long*)&cm.loc->halo_seq;
     unsigned long long bar_seq = ld_volatile_u64(&cm.loc->gs_release);
+    unsigned long long gs_target = ld_volatile_u64(&cm.loc->gs_base);  // one GPU: arrival count that completes the next grid sync (comm.cuh)
     __syncthreads();
 
     const int64_t n = a.n;
@@ -224,7 +225,7 @@ __global__ void __launch_bounds__(ROWS, MINB) bicg_persistent(BicgArgs<R> a, Com
     auto barrier_with_halo = [&](bool pushed) -> bool {
         if (cm.world > 1 && __syncthreads_or(pushed ? 1 : 0)) __threadfence_system();
         halo_seq += 1;
-        return gsync_barrier(cm, hp, bar_seq, cm.world > 1 ? halo_seq : 0ull, s_ctl);
+        return gsync_barrier(cm, hp, bar_seq, cm.world > 1 ? halo_seq : 0ull, s_ctl, gs_target);
     };
     // r = b - A x, r0 = r, returns |r|^2 (both breakdown restarts, BiCGSTAB.h:71-72 and :92; deterministic r0 = r)
     bool x_unset = true;  // x = 0 has not been stored yet
@@ -243,7 +244,7 @@ __global__ void __launch_bounds__(ROWS, MINB) bicg_persistent(BicgArgs<R> a, Com
         if (!barrier_with_halo(pushed)) return false;
         R d[2];
         spmv(a.x, a.t, nullptr, d);
-        if (!gsync_barrier(cm, hp, bar_seq, 0ull, s_ctl)) return false;   // t complete (rows of a tile are not the rows of the vector loop)
+        if (!gsync_barrier(cm, hp, bar_seq, 0ull, s_ctl, gs_target)) return false;   // t complete (rows of a tile are not the rows of the vector loop)
         R rr = (R)0;
         for (int64_t i = gtid; i < n; i += gthreads) {
             const R rn = O::sub(a.b[i], a.t[i]);
@@ -253,7 +254,7 @@ __global__ void __launch_bounds__(ROWS, MINB) bicg_persistent(BicgArgs<R> a, Com
         }
         R t1[1] = {block_sum_n<R, NW>(rr, red)};
         __syncthreads();
-        if (!gsync_allreduce<R, 1, NW>(cm, ar_seq, a.part, t1, red, s_pk, s_ctl)) return false;
+        if (!gsync_allreduce<R, 1, NW>(cm, ar_seq, a.part, t1, red, s_pk, s_ctl, gs_target)) return false;
         rr_out = t1[0];
         return true;
     };
@@ -340,7 +341,7 @@ __global__ void __launch_bounds__(ROWS, MINB) bicg_persistent(BicgArgs<R> a, Com
         spmv(a.y, a.v, a.r0, d);
         block_sum_vec<R, 2, NW>(d, red);
         BICG_STAMP(0)
-        if (!gsync_allreduce<R, 2, NW>(cm, ar_seq, a.part, d, red, s_pk, s_ctl)) {
+        if (!gsync_allreduce<R, 2, NW>(cm, ar_seq, a.part, d, red, s_pk, s_ctl, gs_target)) {
             failed = true;
             break;
         }
@@ -406,7 +407,7 @@ __global__ void __launch_bounds__(ROWS, MINB) bicg_persistent(BicgArgs<R> a, Com
         spmv(a.z, a.t, a.s, d);
         block_sum_vec<R, 2, NW>(d, red);
         BICG_STAMP(0)
-        if (!gsync_allreduce<R, 2, NW>(cm, ar_seq, a.part, d, red, s_pk, s_ctl)) {
+        if (!gsync_allreduce<R, 2, NW>(cm, ar_seq, a.part, d, red, s_pk, s_ctl, gs_target)) {
             failed = true;
             break;
         }
@@ -449,7 +450,7 @@ __global__ void __launch_bounds__(ROWS, MINB) bicg_persistent(BicgArgs<R> a, Com
         R t2[2] = {prr, prho};
         block_sum_vec<R, 2, NW>(t2, red);
         BICG_STAMP(3)
-        if (!gsync_allreduce<R, 2, NW>(cm, ar_seq, a.part, t2, red, s_pk, s_ctl)) {
+        if (!gsync_allreduce<R, 2, NW>(cm, ar_seq, a.part + (size_t)2 * gridDim.x, t2, red, s_pk, s_ctl, gs_target)) {  // not the array of the sync before it (comm.cuh)
             failed = true;
             break;
         }

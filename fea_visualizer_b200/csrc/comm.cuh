@@ -52,6 +52,9 @@ struct CommLocal {  // private to the rank
     unsigned long long err_want;   // the flag value / sequence number that never arrived
     int err_peer;                  // the rank it was expected from
     int err_pad;
+    // one GPU (world == 1): the grid syncs count arrivals on a MONOTONE counter every CTA spins on directly (gsync_* below);
+    // gs_base = its value at the last completed sync, written by that sync's last arrival, read once at kernel start
+    unsigned long long gs_count, gs_base;
 };
 __device__ __forceinline__ void comm_fail(CommLocal* loc, int kind, unsigned long long want, int peer) {
     if (atomicCAS(&loc->error, 0, 1) == 0) {
@@ -277,13 +280,53 @@ __device__ __forceinline__ void sum_cta_partials_vec(const R* part, size_t strid
 // what any CTA of the rank wrote before it is visible to every CTA after it (fence / ticket / LL word / fence).
 // Returns false when a peer never answered (CTA-uniform, and the same in every CTA of the rank: all of them sit in the
 // same sync when a peer dies).  s_ctl[1] must be zero when the kernel starts.
+// One GPU: arrivals are counted on a monotone counter (CommLocal::gs_count) that every CTA spins on directly, so a sync is
+// released by the last ARRIVAL itself, not by a store the last CTA makes after it noticed being last -- one L2 round trip
+// less on the critical path.  `target` = the counter value that completes this sync (kernel-local running value, started
+// from CommLocal::gs_base).  Returns false on timeout.
+__device__ __forceinline__ bool gsync_count_arrive_and_wait(const Comm& cm, unsigned long long target) {
+    const unsigned long long old = atomicAdd(&cm.loc->gs_count, 1ull);
+    if (old + 1 == target) st_volatile_u64(&cm.loc->gs_base, target);  // only the next kernel reads it
+    bool ok = true;
+    if (old + 1 < target && ld_volatile_u64(&cm.loc->gs_count) < target) {
+        const unsigned long long t0 = globaltimer_ns();
+        while (ld_volatile_u64(&cm.loc->gs_count) < target) {
+            if (globaltimer_ns() - t0 > kSpinTimeoutNs || *(volatile int*)&cm.loc->error) {
+                comm_fail(cm.loc, 6, target, cm.rank);
+                ok = false;
+                break;
+            }
+        }
+    }
+    return ok;
+}
+
 template <typename R, int K, int NW>
 __device__ __forceinline__ bool gsync_allreduce(const Comm& cm, unsigned long long& seq, R* __restrict__ part /* K x gridDim.x */,
                                                 R (&v)[K] /* in: this CTA's partials (thread 0); out: the global sums */,
-                                                R* red /* (NW + 1) * K */, double* s_pk /* kMaxRanks * 4 */, int* s_ctl /* 2 */) {
+                                                R* red /* (NW + 1) * K */, double* s_pk /* kMaxRanks * 4 */, int* s_ctl /* 2 */,
+                                                unsigned long long& gtarget /* world == 1: see gsync_count_arrive_and_wait */) {
     static_assert(K >= 1 && K <= 4, "an ArSlot carries four values");
     const unsigned G = gridDim.x;
     seq += 1;
+    if (cm.world == 1) {
+        // Every CTA adds all partials itself, in the order the last CTA of the multi-rank path uses (same bits).  `part` must not
+        // be the array of the PREVIOUS sync of the kernel: a fast CTA writes its next partial while a slow one still reads.
+        gtarget += G;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+#pragma unroll
+            for (int k = 0; k < K; k++) part[(size_t)k * G + blockIdx.x] = v[k];
+            __threadfence();
+            if (!gsync_count_arrive_and_wait(cm, gtarget)) s_ctl[1] = 1;
+            __threadfence();
+        }
+        __syncthreads();
+        sum_cta_partials_vec<R, K, NW>(part, (size_t)G, v, red);
+        const bool failed1 = s_ctl[1] != 0;
+        __syncthreads();
+        return !failed1;
+    }
     __syncthreads();
     if (threadIdx.x == 0) {
 #pragma unroll
@@ -327,9 +370,22 @@ __device__ __forceinline__ bool gsync_allreduce(const Comm& cm, unsigned long lo
 // the neighbours' ghost tails (each pushing CTA ran a system-scope fence before arriving); the last CTA to arrive raises
 // the neighbours' halo flags with release stores, one thread per neighbour, AFTER letting its own rank go on.
 __device__ __forceinline__ bool gsync_barrier(const Comm& cm, const HaloPlan& hp, unsigned long long& bseq, unsigned long long halo_seq,
-                                              int* s_ctl /* 2 */) {
+                                              int* s_ctl /* 2 */, unsigned long long& gtarget) {
     const unsigned G = gridDim.x;
     bseq += 1;
+    if (cm.world == 1) {
+        gtarget += G;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            __threadfence();
+            if (!gsync_count_arrive_and_wait(cm, gtarget)) s_ctl[1] = 1;
+            __threadfence();
+        }
+        __syncthreads();
+        const bool failed1 = s_ctl[1] != 0;
+        __syncthreads();
+        return !failed1;
+    }
     __syncthreads();
     if (threadIdx.x == 0) {
         __threadfence();

@@ -203,7 +203,7 @@ class SolverT final : public SolverBase {
         }
         if (pcg_max_grid_ > 0) {
             opt_.loop_mode = FEAB_LOOP_PERSISTENT;
-            d_ppart_.alloc((size_t)3 * pcg_max_grid_);
+            d_ppart_.alloc((size_t)4 * std::max(pcg_max_grid_, 1024));  // pcg_persistent: 3 x grid; bicg_persistent: 4 x grid
         }
         // Gray-Scott: both solves of a step in lock-step from one index stream (pcg_dual.cuh); FEAB_DUAL=0/1 overrides
         using DCfg = DualCfg<R, kDualRows, kPcgCpr, kPcgStages>;

@@ -70,6 +70,7 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a, Com
     unsigned long long ar_seq = *(volatile unsigned long long*)&cm.loc->ar_seq;
     unsigned long long halo_seq = *(volatile unsigned long long*)&cm.loc->halo_seq;
     unsigned long long bar_seq = ld_volatile_u64(&cm.loc->gs_release);
+    unsigned long long gs_target = ld_volatile_u64(&cm.loc->gs_base);  // one GPU: arrival count that completes the next grid sync (comm.cuh)
     __syncthreads();
     const int64_t n = a.n;
     CgState<R> c2[2];
@@ -255,7 +256,7 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a, Com
         prologue();
         DUAL_STAMP(0)
         DUAL_ARRIVAL(0)
-        if (!gsync_allreduce<R, 2, NWT>(cm, ar_seq, part, pap, red, s_v, s_ctl)) {
+        if (!gsync_allreduce<R, 2, NWT>(cm, ar_seq, part, pap, red, s_v, s_ctl, gs_target)) {
             failed = true;
             break;
         }
@@ -301,7 +302,7 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a, Com
         block_sum_vec<R, 4, NWT>(pb, red);
         DUAL_STAMP(3)
         DUAL_ARRIVAL(2)
-        if (!gsync_allreduce<R, 4, NWT>(cm, ar_seq, part + (size_t)2 * G, pb, red, s_v, s_ctl)) {
+        if (!gsync_allreduce<R, 4, NWT>(cm, ar_seq, part + (size_t)2 * G, pb, red, s_v, s_ctl, gs_target)) {
             failed = true;
             break;
         }
@@ -387,7 +388,7 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a, Com
         if (cm.world == 1) {
             if (fin[0] || fin[1]) break;  // the kernel boundary is the barrier the survivor's next SpMV needs
             DUAL_ARRIVAL(4)
-            if (!gsync_barrier(cm, hp, bar_seq, 0ull, s_ctl)) {
+            if (!gsync_barrier(cm, hp, bar_seq, 0ull, s_ctl, gs_target)) {
                 failed = true;
                 break;
             }
@@ -400,7 +401,7 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a, Com
             if (__syncthreads_or(pushed ? 1 : 0)) __threadfence_system();
             halo_seq += 1;
             DUAL_ARRIVAL(4)
-            if (!gsync_barrier(cm, hp, bar_seq, halo_seq, s_ctl)) {
+            if (!gsync_barrier(cm, hp, bar_seq, halo_seq, s_ctl, gs_target)) {
                 failed = true;
                 break;
             }

@@ -115,6 +115,7 @@ __global__ void __launch_bounds__(ROWS, MINB) pcg_persistent(PcgArgs<R> a, Comm 
     unsigned long long ar_seq = *(volatile unsigned long long*)&cm.loc->ar_seq;
     unsigned long long halo_seq = *(volatile unsigned long long*)&cm.loc->halo_seq;
     unsigned long long bar_seq = ld_volatile_u64(&cm.loc->gs_release);
+    unsigned long long gs_target = ld_volatile_u64(&cm.loc->gs_base);  // one GPU: arrival count that completes the next grid sync (comm.cuh)
     __syncthreads();
 
     // ---- which system, and its state ----
@@ -311,7 +312,7 @@ __global__ void __launch_bounds__(ROWS, MINB) pcg_persistent(PcgArgs<R> a, Comm 
         __syncthreads();
         prologue();  // next iteration's first tiles stream in while phases B / C run
         PCG_STAMP(0)
-        if (!gsync_allreduce<R, 1, NW>(cm, ar_seq, part_pap, pap, red, s_pk, s_ctl)) {
+        if (!gsync_allreduce<R, 1, NW>(cm, ar_seq, part_pap, pap, red, s_pk, s_ctl, gs_target)) {
             failed = true;
             break;
         }
@@ -348,7 +349,7 @@ __global__ void __launch_bounds__(ROWS, MINB) pcg_persistent(PcgArgs<R> a, Comm 
         R t2[2] = {prr, prz};
         block_sum_vec<R, 2, NW>(t2, red);
         PCG_STAMP(3)
-        if (!gsync_allreduce<R, 2, NW>(cm, ar_seq, part_rr, t2, red, s_pk, s_ctl)) {  // part_rz = part_rr + gridDim.x
+        if (!gsync_allreduce<R, 2, NW>(cm, ar_seq, part_rr, t2, red, s_pk, s_ctl, gs_target)) {  // part_rz = part_rr + gridDim.x
             failed = true;
             break;
         }
@@ -425,7 +426,7 @@ __global__ void __launch_bounds__(ROWS, MINB) pcg_persistent(PcgArgs<R> a, Comm 
         if (cm.world > 1 && __syncthreads_or(pushed ? 1 : 0)) __threadfence_system();
         PCG_STAMP(6)
         halo_seq += 1;
-        if (!gsync_barrier(cm, hp, bar_seq, cm.world > 1 ? halo_seq : 0ull, s_ctl)) {
+        if (!gsync_barrier(cm, hp, bar_seq, cm.world > 1 ? halo_seq : 0ull, s_ctl, gs_target)) {
             failed = true;
             break;
         }
