@@ -213,7 +213,7 @@ class SolverT final : public SolverBase {
         dual_max_grid_ = coop ? docc * sms_ : 0;
         if (dual_max_grid_ > 0) d_dpart_.alloc((size_t)6 * dual_max_grid_);
         if (const char* v = getenv("FEAB_DUAL")) dual_ = atoi(v) != 0;
-        if (const char* v = getenv("FEAB_ZIGZAG")) zigzag_ = atoi(v) != 0 ? 1 : 0;
+        if (const char* v = getenv("FEAB_ZIGZAG")) zigzag_ = std::max(0, std::min(2, atoi(v)));
         if (const char* v = getenv("FEAB_COOP")) coop_launch_ = atoi(v) != 0;
         // non-symmetric mode: the whole BiCGSTAB solve as one cooperative kernel (bicg_persistent.cuh), same tile geometry
         CK(cudaFuncSetAttribute(bicg_persistent<R, kPcgRows, kPcgCpr, kPcgStages, kPcgMinB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -1164,6 +1164,15 @@ class SolverT final : public SolverBase {
         return dual_ && !capturing && opt_.loop_mode == FEAB_LOOP_PERSISTENT && eq_ == FEAB_EQ_REACTION_DIFFUSION && dual_max_grid_ > 0 &&
                !use_bicgstab();
     }
+    // Order of phase C of the persistent PCG kernels (PcgArgs::zigzag).  Measured (profiles/r02_v17_*, r02_v18_*, r02_v19_*): plain
+    // ascending is the fastest on one GPU (53.95 vs 52.3 steps/s at 16 M rows against descending) and at 8 M rows per rank
+    // (N = 2: 103.5 vs 100.1 against both orders that start on the boundary rows); at 2 M rows per rank starting on the
+    // boundary rows costs nothing (357.0 vs 357.3) and puts their NVLink pushes ahead of the interior.  Decided from the rows
+    // per rank of the whole mesh, so that every rank of a partition takes the same order.
+    int phase_c_order() const {
+        if (zigzag_ >= 0) return zigzag_;
+        return world_ > 1 && nglob_ / world_ <= 3000000 ? 2 : 0;
+    }
     // Gray-Scott: u- and v-solve advance together until the first of them stops (pcg_dual.cuh); the single-system kernel
     // then finishes whichever is still running (it picks the system from CgState; both done -> it returns at once).
     // Two launches per step; the start of both solves (thresholds, early-outs) is taken inside pcg_dual.
@@ -1187,7 +1196,7 @@ class SolverT final : public SolverBase {
         da.first_halo_tile = first_halo_tile(kDualRows);
         da.tol = tol();
         da.maxit = maxit();
-        da.zigzag = zigzag_;
+        da.zigzag = phase_c_order();
         da.prof = prof_dual_ ? d_prof_ : nullptr;
         da.arrivals = nullptr;
         if (prof_arrivals_) {
@@ -1229,7 +1238,7 @@ class SolverT final : public SolverBase {
         pa.begin = begin;
         pa.tol = tol();
         pa.maxit = maxit();
-        pa.zigzag = zigzag_;
+        pa.zigzag = phase_c_order();
         pa.prof = prof_dual_ ? nullptr : d_prof_;
         const int grid = std::min(pcg_max_grid_, pa.num_tiles);
         using PCfg = TmaCfg<R, kPcgRows, kPcgCpr, kPcgStages>;
@@ -2024,7 +2033,7 @@ class SolverT final : public SolverBase {
     int cluster_ent_max_ = 0;
     int grid_cap_ = INT32_MAX;
     bool coop_launch_ = true;  // FEAB_COOP=0: plain launches of the persistent kernels (launch_resident)
-    int zigzag_ = 1;     // FEAB_ZIGZAG=0: phase C of the persistent kernels walks the rows ascending (boundary rows and their NVLink pushes last)
+    int zigzag_ = -1;    // FEAB_ZIGZAG: order of phase C of the persistent PCG kernels (PcgArgs::zigzag); -1 = phase_c_order() decides
     bool dual_ = true;   // FEAB_DUAL=0 runs the two Gray-Scott solves one after the other
     bool dual_last_ = false;
     DevBuf<R> d_dpart_;

@@ -139,6 +139,7 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a, Com
     const int64_t nvec = n / N;
     const int64_t gthreads = (int64_t)gridDim.x * blockDim.x;
     const int64_t gtid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t c_start = (a.zigzag == 2 && cm.world > 1) ? (min(nvec, (int64_t)hp.n_int / N) & ~(int64_t)63) : 0;  // see PcgArgs::zigzag
     const R* const Ah = a.A[h];
     R* const ph = a.p[h];
     R* const yh = a.y[h];
@@ -346,7 +347,9 @@ __global__ void __launch_bounds__(2 * ROWS, MINB) pcg_dual(PcgDualArgs<R> a, Com
                 const R* const rs = a.r[s];
                 const R* const ds = a.dinv[s];
                 for (int64_t j = gtid; j < nvec; j += gthreads) {
-                    const int64_t i = a.zigzag ? nvec - 1 - j : j;
+                    int64_t i = j + c_start;  // ascending, boundary rows (the last ones) first on a partition
+                    if (i >= nvec) i -= nvec;
+                    if (a.zigzag == 1) i = nvec - 1 - j;
                     R xv[N], rv[N], pv[N], dv[N];
                     if (first) {
 #pragma unroll

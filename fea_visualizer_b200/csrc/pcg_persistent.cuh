@@ -44,8 +44,10 @@ struct PcgArgs {
                        // from the RHS kernel's published sums (mailbox all-reduce number ar_seq); 0: CgState is already set
     R tol;
     int maxit;
-    int zigzag;        // phase C walks the rows DESCENDING: the boundary rows (last), whose new p goes to the neighbours over NVLink,
-                       // come first, so the remote stores are long acknowledged when the CTA fences before the grid sync; FEAB_ZIGZAG=0: ascending
+    int zigzag;        // order of phase C.  0: ascending.  2: ascending, but starting at the boundary rows (numbered last) and wrapping
+                       // round, so that their new p is on its way to the neighbours over NVLink while the interior is updated.
+                       // 1: DESCENDING (boundary rows first, and the rows phase B touched last) -- 13 % slower in that phase
+                       // (208 vs 240 us at 16 M rows, profiles/r02_v17_*).  feab.cu phase_c_order() picks 0 or 2; FEAB_ZIGZAG
     unsigned long long* prof; // optional (FEAB_PCG_PROF=1): ns spent by CTA 0 in [A, sync1 (barrier + all-reduce of p.Ap), -, B, sync2, -, C, sync3, -], iterations
 };
 
@@ -203,6 +205,7 @@ __global__ void __launch_bounds__(ROWS, MINB) pcg_persistent(PcgArgs<R> a, Comm 
     const int64_t nvec = n / N;
     const int64_t gthreads = (int64_t)gridDim.x * blockDim.x;
     const int64_t gtid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t c_start = (a.zigzag == 2 && cm.world > 1) ? (min(nvec, (int64_t)hp.n_int / N) & ~(int64_t)63) : 0;  // first 16-byte vector of phase C
 
     // partitioned solve: mirror a boundary row's new p on every neighbour that keeps it as a ghost
     auto push_row = [&](int64_t row, R val) {
@@ -386,7 +389,9 @@ __global__ void __launch_bounds__(ROWS, MINB) pcg_persistent(PcgArgs<R> a, Comm 
         abs_old = rz;
         bool pushed = false;
         for (int64_t j = gtid; j < nvec; j += gthreads) {
-            const int64_t i = a.zigzag ? nvec - 1 - j : j;
+            int64_t i = j + c_start;  // ascending, boundary rows (the last ones) first on a partition
+            if (i >= nvec) i -= nvec;
+            if (a.zigzag == 1) i = nvec - 1 - j;
             R xv[N], rv[N], pv[N], dv[N];
             if (first) {
 #pragma unroll
