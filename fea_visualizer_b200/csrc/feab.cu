@@ -1164,15 +1164,10 @@ class SolverT final : public SolverBase {
         return dual_ && !capturing && opt_.loop_mode == FEAB_LOOP_PERSISTENT && eq_ == FEAB_EQ_REACTION_DIFFUSION && dual_max_grid_ > 0 &&
                !use_bicgstab();
     }
-    // Order of phase C of the persistent PCG kernels (PcgArgs::zigzag).  Measured (profiles/r02_v17_*, r02_v18_*, r02_v19_*): plain
-    // ascending is the fastest on one GPU (53.95 vs 52.3 steps/s at 16 M rows against descending) and at 8 M rows per rank
-    // (N = 2: 103.5 vs 100.1 against both orders that start on the boundary rows); at 2 M rows per rank starting on the
-    // boundary rows costs nothing (357.0 vs 357.3) and puts their NVLink pushes ahead of the interior.  Decided from the rows
-    // per rank of the whole mesh, so that every rank of a partition takes the same order.
-    int phase_c_order() const {
-        if (zigzag_ >= 0) return zigzag_;
-        return world_ > 1 && nglob_ / world_ <= 3000000 ? 2 : 0;
-    }
+    // Order of phase C of the persistent PCG kernels (PcgArgs::zigzag).  Measured (profiles/r02_v17_*, r02_v18_*, r02_v19_*, r02_v20_*):
+    // plain ascending is the fastest everywhere -- one GPU 53.95 vs 52.3 steps/s at 16 M rows against descending, N = 2 103.5
+    // vs 100.1, N = 8 342.2 vs 325.0 against the order that starts on the boundary rows.
+    int phase_c_order() const { return zigzag_ >= 0 ? zigzag_ : 0; }
     // Gray-Scott: u- and v-solve advance together until the first of them stops (pcg_dual.cuh); the single-system kernel
     // then finishes whichever is still running (it picks the system from CgState; both done -> it returns at once).
     // Two launches per step; the start of both solves (thresholds, early-outs) is taken inside pcg_dual.

@@ -47,7 +47,7 @@ struct PcgArgs {
     int zigzag;        // order of phase C.  0: ascending.  2: ascending, but starting at the boundary rows (numbered last) and wrapping
                        // round, so that their new p is on its way to the neighbours over NVLink while the interior is updated.
                        // 1: DESCENDING (boundary rows first, and the rows phase B touched last) -- 13 % slower in that phase
-                       // (208 vs 240 us at 16 M rows, profiles/r02_v17_*).  feab.cu phase_c_order() picks 0 or 2; FEAB_ZIGZAG
+                       // (208 vs 240 us at 16 M rows, profiles/r02_v17_*).  Default 0: also at N = 8 it beats 2 (342 vs 325 steps/s); FEAB_ZIGZAG
     unsigned long long* prof; // optional (FEAB_PCG_PROF=1): ns spent by CTA 0 in [A, sync1 (barrier + all-reduce of p.Ap), -, B, sync2, -, C, sync3, -], iterations
 };
 
