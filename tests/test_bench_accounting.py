@@ -40,3 +40,24 @@ def test_solve_traffic_file_matches_the_metric_workload():
 def test_measured_peak_has_a_source():
     peak, src = bench.measured_peak()
     assert 5000.0 < peak < 8000.0 and ("measured" in src or "fallback" in src)
+
+
+def test_final_build_ncu_capture_agrees_with_the_traffic_model():
+    """profiles/r02_v22_ncu_full.json: `ncu --set full` of one pcg_dual and one pcg_persistent launch of the FINAL round-2 build.
+    Their DRAM bytes must be a whole number of passes of the per-pass figures bench.py scales (profiles/r02_solve_traffic.json,
+    captured on an earlier build): the kernels changed (row order of phase C, one-GPU syncs), the traffic did not."""
+    cap = json.load(open(os.path.join(ROOT, "profiles", "r02_v22_ncu_full.json")))
+    raw = json.load(open(os.path.join(ROOT, "profiles", "r02_solve_traffic.json")))
+    assert cap["rows"] == raw["rows"] == ROWS_16M
+    passes = {}
+    for kernel, fit in (("pcg_dual", raw["dual"]), ("pcg_persistent", raw["single"])):
+        k = cap["kernels"][kernel]
+        total = k["dram_bytes_read"] + k["dram_bytes_write"]
+        p = (total - fit["fixed_bytes"]) / fit["bytes_per_pass"]
+        passes[kernel] = round(p)
+        assert abs(p - round(p)) < 0.15, (kernel, p)               # within 1 % of a whole number of passes
+        gbps = total / k["duration_ms"] / 1e6
+        assert gbps > 5800.0, (kernel, gbps)                       # 6 228 / 6 030 GB/s: 0.95 / 0.92 of the 6 551.7 GB/s copy peak of that pool
+        assert k["registers"] == 64 and k["grid"] == 296 and k["block"] == 512   # 2 resident CTAs per SM x 148 SMs
+    # the captured step is one of the seed-protocol steps: the u solve stops first, the tail finishes the v solve
+    assert 15 <= passes["pcg_dual"] <= 19 and 5 <= passes["pcg_persistent"] <= 9
