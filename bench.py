@@ -420,6 +420,12 @@ def main():
     t0 = time.perf_counter()
     F = make_handle(xyz, tri, ob)
     setup_s = time.perf_counter() - t0
+    try:
+        # device memory in use on this rank's GPU once the handle exists (cudaMemGetInfo: CUDA context + mesh + matrices + vectors)
+        free_b, total_b = torch.cuda.mem_get_info(local_rank)
+        mem_used_gb = (total_b - free_b) / 1e9
+    except Exception:
+        mem_used_gb = -1.0
     _, n, nnz, max_row = F.counts()           # this rank's rows / entries
     lay = F.mg_layout()
     F.set_equation(EQ_GS)
@@ -486,12 +492,12 @@ def main():
         sys.stderr.write(f"[rank {rank}] step phases (ms): {json.dumps(step_ms)}\n")
     clocks = sampler.stop() if rank == 0 else None
 
-    t = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
+    t = torch.tensor([ms, e2e_s * 1e3, mem_used_gb], dtype=torch.float64, device="cuda")
     tot = torch.tensor([n, nnz, lay["n_ghost"], launches], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(tot)
-    ms_max, e2e_ms_max = t.tolist()
+    ms_max, e2e_ms_max, mem_used_gb_max = t.tolist()
     n_all, nnz_all, ghosts_all, launches_all = (int(x) for x in tot.tolist())
     rb = 8 if args.real == 64 else 4
     # algorithmic bytes of one Gray-Scott step: fused RHS + (it_u + it_v) PCG iterations
@@ -573,6 +579,7 @@ def main():
                            "tolerance": "eps of dtype (Eigen default)" if args.tol < 0 else args.tol,
                            "pcg_iterations_last_step": its, "spmv_passes_last_step": passes, "loop": args.loop, "solve_kernel": solve_kernel,
                            "l2_policy": "inputs larger than L2 (matrix + vectors >> 126 MB)", "setup_s": setup_s,
+                           "device_mem_used_gb_max_over_ranks": round(mem_used_gb_max, 3) if mem_used_gb_max >= 0 else None,
                            "timed_steps": f"steps {warm}..{warm + args.steps - 1} of the run, in both legs (state restored from a snapshot in between)"},
                 "us_per_pcg_iteration": (solve_ms * 1e3 / max(1, its[0] + its[1])) if solve_ms else None,
                 "e2e": {"value": e2e_value, "unit": "steps/s", "h2d_bytes_per_step": 4 * V, "d2h_bytes_per_step": 4 * V,
