@@ -8,7 +8,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libfeab.so")
-SOURCES = ["feab.cu", "surface.cu", "ply_writer.cpp"]
+SOURCES = ["feab.cu", "surface.cu", "noalloc.cu", "ply_writer.cpp"]
 
 
 def _deps():

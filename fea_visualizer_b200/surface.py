@@ -18,11 +18,33 @@ ABI_SYMBOLS = [
     "feas_create", "feas_destroy", "feas_last_error", "feas_set_mesh", "feas_detect_boundary", "feas_load_obj", "feas_get_counts",
     "feas_get_mesh", "feas_set_values", "feas_get_values", "feas_set_values_device", "feab_values_device", "feas_set_color_map", "feas_color_map",
     "feas_smooth_normals", "feas_pick", "feas_brush", "feas_ply_build", "feas_ply_fetch", "feas_export_ply", "feas_write_ply", "feas_parse_obj", "feas_last_ms",
+    "feas_detect_boundary_noalloc",
 ]
+
+
+NOALLOC_MAX_TRIANGLES = 349525     # FEAS_NOALLOC_MAX_TRIANGLES, include/feab_surface.h
 
 
 def _p(a):
     return None if a is None else C.c_void_p(a.ctypes.data)
+
+
+def detect_boundary_noalloc(device, stream, num_vertices, num_triangles, tri_device_ptr, on_boundary_device_ptr):
+    """feas_detect_boundary_noalloc: boundary flags for a caller that owns its device buffers and must not allocate.
+    `tri_device_ptr` / `on_boundary_device_ptr` are raw device addresses (ints) of memory the CALLER allocated, `stream`
+    a raw cudaStream_t or 0.  Nothing is allocated on the way, here or in the library: the edge table is a fixed array
+    inside libfeab (at most NOALLOC_MAX_TRIANGLES triangles).  Blocks until the flags are written; returns the number of
+    boundary vertices.  Raises FeabError with the library's message otherwise."""
+    lib = load_library()
+    fn = lib.feas_detect_boundary_noalloc
+    fn.restype = C.c_int
+    fn.argtypes = [C.c_int, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.POINTER(C.c_int64), C.c_char_p, C.c_int64]
+    nb = C.c_int64(-1)
+    err = C.create_string_buffer(512)
+    rc = fn(device, stream or None, num_vertices, num_triangles, tri_device_ptr or None, on_boundary_device_ptr or None, C.byref(nb), err, 512)
+    if rc != 0:
+        raise FeabError(rc, err.value.decode())
+    return nb.value
 
 
 def write_ply(path, positions, colors, tri):

@@ -94,6 +94,29 @@ int feas_pick(FeasHandle* h, const float* origin3, const float* direction3, int*
  * solver with feab_brush(solver, &node, 1, value), like Application does through surface->values. */
 int feas_brush(FeasHandle* h, const float* origin3, const float* direction3, float value, int* node_out);
 
+/* N2 once more, for callers that must not allocate GPU memory.  No counterpart in the reference (its Surface owns its own
+ * std::map and its own GL buffers); added for host programs that cannot afford feas_detect_boundary's per-call
+ * cudaMalloc/cudaFree of the edge table: a render loop that the device-wide synchronisation of cudaMalloc would stall, a
+ * plugin inside an application whose memory pool already owns all of the GPU, code that is forbidden to enter the CUDA
+ * allocator after start-up.  The entry point allocates NOTHING (no cudaMalloc/cudaFree, no allocating library call, no
+ * handle): the caller passes device buffers it already owns, and the edge table lives in a fixed 24 MiB array inside
+ * libfeab's device image, which every GPU that loads the library holds until the process exits.
+ *   device               CUDA ordinal the two buffers live on (made current for the call, the caller's device is restored)
+ *   stream               a cudaStream_t, or NULL for the default stream; the call WAITS for it before returning
+ *   tri_device           num_triangles x 3 uint32, device memory (may be NULL when num_triangles == 0)
+ *   on_boundary_device   num_vertices bytes, device memory; overwritten with 0 / 1 like feas_detect_boundary's output
+ *   num_boundary_points  host, optional: how many flags are set (0 = closed mesh)
+ *   errbuf / errbuf_len  host, optional: receives the message when the return value is not 0 (there is no handle to ask)
+ * Limits and rules: num_triangles <= FEAS_NOALLOC_MAX_TRIANGLES, larger meshes are refused with FEAB_EINVAL (use
+ * feas_detect_boundary); a triangle index >= num_vertices is reported as FEAB_EINVAL instead of being written out of
+ * bounds.  All calls on a device share the one table, which still holds the previous call's edges: each call wipes what it
+ * needs first, and two calls running on the GPU at the same time would corrupt each other -- the library serialises its
+ * callers with a lock and the final wait, so expect no concurrency from it.  The first call on a device also looks up the
+ * table's device address (one-time set-up): make that call before the process begins any stream capture. */
+#define FEAS_NOALLOC_MAX_TRIANGLES 349525   /* 6 x triangles <= 2^21 table slots (load factor <= 0.5) */
+int feas_detect_boundary_noalloc(int device, void* stream, int64_t num_vertices, int64_t num_triangles, const uint32_t* tri_device,
+                                 uint8_t* on_boundary_device, int64_t* num_boundary_points, char* errbuf, int64_t errbuf_len);
+
 /* measurement: device milliseconds of the last feas_ply_build / feas_detect_boundary / feas_smooth_normals / feas_pick (CUDA events
  * on the Surface's stream), and the number of kernels this handle has launched */
 int feas_last_ms(const FeasHandle* h, double* ms, int64_t* kernel_launches);
