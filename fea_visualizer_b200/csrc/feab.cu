@@ -215,6 +215,7 @@ class SolverT final : public SolverBase {
         if (const char* v = getenv("FEAB_DUAL")) dual_ = atoi(v) != 0;
         if (const char* v = getenv("FEAB_ZIGZAG")) zigzag_ = std::max(0, std::min(2, atoi(v)));
         if (const char* v = getenv("FEAB_COOP")) coop_launch_ = atoi(v) != 0;
+        if (const char* v = getenv("FEAB_FAULT_GSYNC")) fault_gsync_call_ = atoi(v);  // test hook, see step()
         // non-symmetric mode: the whole BiCGSTAB solve as one cooperative kernel (bicg_persistent.cuh), same tile geometry
         CK(cudaFuncSetAttribute(bicg_persistent<R, kPcgRows, kPcgCpr, kPcgStages, kPcgMinB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)PCfg::kSmemBytes));
@@ -960,7 +961,9 @@ class SolverT final : public SolverBase {
         CK(cudaSetDevice(device_));
         int f = 0;
         CK(cudaMemcpy(&f, d_unstable_, sizeof(int), cudaMemcpyDeviceToHost));
-        return f != 0 && f == last_stamp_;  // finish_step stamps the flag with the step number: set by the LAST step only
+        // finish_step stamps the flag with the step number (atomicMax keeps the latest unstable step): true when ANY step of the
+        // last feab_step call went unstable -- the reference tests after every advance_time (src/Application.cpp:532-533)
+        return f != 0 && call_first_stamp_ != 0 && f >= call_first_stamp_;
     }
 
     // ---------------------------------------------------------------- operator cache (K2)
@@ -1065,7 +1068,6 @@ class SolverT final : public SolverBase {
         // upload, ...): the solver's own result is re-read through float by the RHS kernel (solver.cuh through_float).  A
         // captured graph and the lock-step test driver always gather.
         const bool gather = values_dirty_ || capturing || lockstep_;
-        if (capturing) CK(cudaMemsetAsync(d_unstable_, 0, sizeof(int), s));
         if (gather) {
             R* target = eq_ == FEAB_EQ_REACTION_DIFFUSION ? d_v_.p : d_u_.p;
             if (world_ > 1) wait_kernel<<<1, 32, 0, s>>>(cm_, hp_, 1);  // ghost values: the neighbours' end-of-step pushes have landed
@@ -1123,8 +1125,17 @@ class SolverT final : public SolverBase {
     void ph_finish(cudaStream_t s, bool capturing) {
         const int gV = cdiv64(V_, kBlock);
         // a captured graph replays one stamp: it keeps the sticky semantics of a flag that is reset by feab_clear only
-        const int stamp = capturing ? 1 : (step_stamp_ = step_stamp_ >= INT32_MAX - 1 ? 1 : step_stamp_ + 1);
-        if (!capturing) last_stamp_ = stamp;
+        // a captured graph replays one stamp; step() clears the flag once before it launches the graphs of a call
+        if (!capturing && step_stamp_ >= INT32_MAX - 1) {  // only the lock-step driver gets here: step() wraps at the start of a call
+            CK(cudaMemsetAsync(d_unstable_, 0, sizeof(int), s));
+            step_stamp_ = 0;
+            call_first_stamp_ = 0;
+        }
+        const int stamp = capturing ? 1 : ++step_stamp_;
+        if (!capturing) {
+            last_stamp_ = stamp;
+            if (!call_first_stamp_) call_first_stamp_ = stamp;
+        }
         if (world_ > 1)
             finish_rows<R><<<std::max(1, std::min({cdiv64(n_, kBlock), sms_ * 4, grid_cap_})), kBlock, 0, s>>>(
                 d_values_.p, node_of_col_p_, n_, d_dir_nodes_.p, n_dir_, d_u_.p, d_v_.p, eq_ == FEAB_EQ_WAVE ? 1 : 0, (R)scalars().dt,
@@ -1347,8 +1358,8 @@ class SolverT final : public SolverBase {
         ca.nsteps = nsteps;
         ca.st = d_st_;
         ca.unstable = d_unstable_;
-        if ((int64_t)step_stamp_ + nsteps >= INT32_MAX - 1) step_stamp_ = 0;
-        ca.stamp0 = step_stamp_ + 1;
+        ca.stamp0 = step_stamp_ + 1;  // step() made room for nsteps stamps
+        if (!call_first_stamp_) call_first_stamp_ = ca.stamp0;
         ca.col_cap = col_cap;
         ca.prof = prof_dual_ ? nullptr : d_prof_;
         ca.val_cap = val_cap;
@@ -1498,14 +1509,18 @@ class SolverT final : public SolverBase {
         }
     }
     void check_comm_error() {
-        if (world_ == 1) return;
+        // One GPU too: the grid syncs of the persistent kernels are bounded spins of their own (comm.cuh kind 6) and fail closed
+        // exactly like a lost peer does -- without this check a timed-out solve would leave the handle frozen and silent.
         CommLocal l;
         CK(cudaMemcpy(&l, d_loc_, sizeof(l), cudaMemcpyDeviceToHost));
         if (l.error) {
-            // the grid-sync / ticket counters of the kernels that gave up are meaningless now
+            // the grid-sync / ticket counters of the kernels that gave up are meaningless now: the monotone one-GPU counter
+            // stopped short of a sync, so it restarts from zero together with its base (the next kernel reads gs_base first)
             l.error = 0;
             l.ticket = 0;
             l.gs_arrive = 0;
+            l.gs_count = 0;
+            l.gs_base = 0;
             const int kind = l.err_kind, peer = l.err_peer;
             const unsigned long long want = l.err_want;
             l.err_kind = 0;
@@ -1540,6 +1555,13 @@ class SolverT final : public SolverBase {
         // that call, i.e. after the peers' last read of their mirrors.
         const bool root_mode = world_ > 1 && sync == FEAB_SYNC_ROOT && values != nullptr;
         if (values) values_dirty_ = true;
+        // instability stamps of this call: [call_first_stamp_, step_stamp_].  The stamp counter restarts (with a cleared flag)
+        // BEFORE a call that would run past INT32_MAX, never inside one: atomicMax would keep a pre-wrap value for ever.
+        call_first_stamp_ = 0;
+        if ((int64_t)step_stamp_ + nsteps >= INT32_MAX - 1) {
+            CK(cudaMemsetAsync(d_unstable_, 0, sizeof(int), stream_));
+            step_stamp_ = 0;
+        }
         mark_now_ = true;
         mark(0);
         mark_now_ = false;
@@ -1559,6 +1581,16 @@ class SolverT final : public SolverBase {
             CK(cudaMemcpyAsync(d_values_.p, values, V_ * sizeof(float), cudaMemcpyHostToDevice, stream_));
         }
         if (n_ > 0 && nsteps > 0) {
+            // Fault injection for the tests (FEAB_FAULT_GSYNC=k at feab_create): before the k-th stepping call of this handle one
+            // arrival is taken away from the one-GPU grid-sync counter (its base moves up by one), i.e. one CTA "never arrives":
+            // the first grid sync of that call runs into its bounded wait and the call must end in FEAB_ECOMM.
+            if (fault_gsync_call_ > 0 && ++step_calls_ == fault_gsync_call_) {
+                CK(cudaStreamSynchronize(stream_));
+                CommLocal l;
+                CK(cudaMemcpy(&l, d_loc_, sizeof(l), cudaMemcpyDeviceToHost));
+                l.gs_base += 1;
+                CK(cudaMemcpy(d_loc_, &l, sizeof(l), cudaMemcpyHostToDevice));
+            }
             ensure_operator();
             ph_push_state(stream_);
             // a device without cooperative launch runs BiCGSTAB through the WHILE graph
@@ -1566,7 +1598,9 @@ class SolverT final : public SolverBase {
             graph_mode_last_ = graph_mode;
             if (graph_mode) {
                 dual_last_ = false;  // a graph replays separate solves
-                last_stamp_ = 1;     // ... and one instability stamp (the graph resets the flag at its head)
+                last_stamp_ = 1;     // ... and one instability stamp: cleared here once per call, sticky over the call's graphs
+                call_first_stamp_ = 1;
+                CK(cudaMemsetAsync(d_unstable_, 0, sizeof(int), stream_));
             }
             if (graph_mode && (!graph_exec_ || graph_eq_ != eq_)) build_graph();
             cluster_steps_last_ = 0;
@@ -1633,14 +1667,18 @@ class SolverT final : public SolverBase {
             cudaGetLastError();
             time_solves_ = false;
         }
-        check_comm_error();
         if (cluster_steps_last_ > 0 && h_flag_[8]) {  // pair mode of pcg_cluster: the other cluster never arrived
             const int who = h_flag_[8];
             h_flag_[8] = 0;
             CK(cudaMemset(&d_loc_->error, 0, sizeof(int)));
+            // the launch was accounted for in full (xbar_count_ += 4 nsteps) but the device counter stopped short: start both
+            // from zero again, or every later pair launch would wait for arrivals that never come
+            CK(cudaMemset(d_xbar_, 0, sizeof(unsigned long long)));
+            xbar_count_ = 0;
             throw Err{FEAB_ECOMM, "step: cluster " + std::to_string(who - 1) + " of the small-mesh kernel timed out waiting for the other cluster; "
                                   "the fields of this call are not valid (FEAB_CLUSTER_PAIR=0 runs the two solves in one cluster)"};
         }
+        check_comm_error();
     }
 
     void read_states(CgState<R>* st2, BicgState<R>* bst) {
@@ -1907,6 +1945,7 @@ class SolverT final : public SolverBase {
         CK(cudaStreamSynchronize(stream_));
         ls_stream_ = shared ? shared : stream_;
         lockstep_ = true;
+        call_first_stamp_ = 0;
         ensure_operator_on(ls_stream_);
         return ls_stream_;
     }
@@ -2027,6 +2066,7 @@ class SolverT final : public SolverBase {
     int64_t cluster_ent_key_ = -1;
     int cluster_ent_max_ = 0;
     int grid_cap_ = INT32_MAX;
+    int fault_gsync_call_ = 0, step_calls_ = 0;  // FEAB_FAULT_GSYNC (test hook)
     bool coop_launch_ = true;  // FEAB_COOP=0: plain launches of the persistent kernels (launch_resident)
     int zigzag_ = -1;    // FEAB_ZIGZAG: order of phase C of the persistent PCG kernels (PcgArgs::zigzag); -1 = phase_c_order() decides
     bool dual_ = true;   // FEAB_DUAL=0 runs the two Gray-Scott solves one after the other
@@ -2053,6 +2093,7 @@ class SolverT final : public SolverBase {
     int64_t launches_ = 0;
     bool values_dirty_ = true;            // surface->values was written by somebody other than finish_step since the last step
     int step_stamp_ = 0, last_stamp_ = 0; // instability flag stamps (finish_step)
+    int call_first_stamp_ = 0;            // stamp of the first step of the last feab_step call (0: no step yet)
 };
 
 // ---------------------------------------------------------------- BiCGSTAB driver

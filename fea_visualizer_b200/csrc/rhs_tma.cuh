@@ -28,7 +28,7 @@ __global__ void __launch_bounds__(ROWS, MINB)
     auto stage_col = [&](int s) { return reinterpret_cast<int*>(base + (size_t)s * Cfg::kStageBytes + Cfg::kValBytes); };
     auto stage_rp = [&](int s) { return reinterpret_cast<int*>(base + (size_t)s * Cfg::kStageBytes + Cfg::kValBytes + Cfg::kColBytes); };
 
-    if (cm.world > 1 && comm_failed(cm)) return;  // fail closed (comm.cuh)
+    if (comm_failed(cm)) return;  // fail closed (comm.cuh), one GPU included: a timed-out grid sync sets the same flag
     uint64_t policy = 0;
     if (threadIdx.x == 0) {
         for (int s = 0; s < STAGES; s++) mbar_init(&full[s], 1);
@@ -60,6 +60,15 @@ __global__ void __launch_bounds__(ROWS, MINB)
     if (cm.world > 1) {
         if (threadIdx.x == 0) wait_flags(cm, hp, 1, *(volatile unsigned long long*)&cm.loc->state_seq);
         __syncthreads();
+        if (comm_failed(cm)) {
+            // the neighbours' u / v never arrived: build nothing, push nothing (comm.cuh contract).  The bulk copies already
+            // issued still target this CTA's shared memory: wait them out before the CTA may exit.
+            if (threadIdx.x == 0) {
+                int t = blockIdx.x;
+                for (int s = 0; s < STAGES && t < num_tiles; s++, t += gridDim.x) mbar_wait(&full[s], 0u);
+            }
+            return;
+        }
     }
     // the vector surface->values feeds (u; Gray-Scott: v) is read through float (solver.cuh through_float)
     auto ldu = [&](int64_t c) { return EQ == 3 ? u[c] : through_float(u[c]); };

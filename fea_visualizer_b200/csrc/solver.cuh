@@ -55,7 +55,7 @@ __global__ void gather_values(const float* __restrict__ values, const int* __res
                               HaloPlan hp) {
     // partitioned: the ghost entries of values come from the neighbours' end-of-step pushes; the caller launches
     // wait_kernel(state) first (one CTA spins, not V / 256 of them)
-    if (cm.world > 1 && comm_failed(cm)) return;
+    if (comm_failed(cm)) return;
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < V) {
         int m = colmap[i];  // idx_map on one GPU; owned + ghost columns on a partition
@@ -575,7 +575,7 @@ __global__ void __launch_bounds__(kBlock) finish_step(float* __restrict__ values
                                                       const int* __restrict__ rowmap, int64_t V, R* __restrict__ u, R* __restrict__ v,
                                                       int wave, R dt, int sol_is_v, int* __restrict__ unstable, int stamp, Comm cm,
                                                       HaloPlan hp) {
-    if (cm.world > 1 && comm_failed(cm)) return;  // fail closed: a solve that lost a peer writes nothing back
+    if (comm_failed(cm)) return;  // fail closed: a solve that lost a peer writes nothing back
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     bool bad = false, pushed = false;
     if (i < V) {
