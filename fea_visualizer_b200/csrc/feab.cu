@@ -1735,7 +1735,8 @@ class SolverT final : public SolverBase {
         REQUIRE(have_mesh_ && n_ > 0, FEAB_ENOMESH, "time_kernel: no mesh");
         REQUIRE(reps > 0 && kernel >= 0 && kernel <= 3, FEAB_EINVAL, "time_kernel: bad arguments");
         REQUIRE(world_ == 1, FEAB_EINVAL, "time_kernel: single-GPU handles only (partitioned kernels wait for their peers)");
-        const Comm one;
+        Comm one;            // a one-GPU communicator of its own ...
+        one.loc = d_loc_;    // ... with the handle's flags behind it: every kernel reads CommLocal::error (fail closed)
         CK(cudaSetDevice(device_));
         ensure_operator();
         const double n = (double)n_, nnz = (double)nnz_, rb = sizeof(R);

@@ -81,3 +81,25 @@ def test_unstable_reports_an_excursion_in_any_step_of_the_call(monkeypatch):
         F.step(2)
         assert not F.unstable(), cluster
         F.close()
+
+
+@pytest.mark.parametrize("real", [64, 32])
+def test_measurement_hook_runs_every_kernel(real, monkeypatch):
+    """feab_time_kernel (bench.py's per-kernel timings) launches the SpMV, the two PCG vector kernels and the RHS build of
+    every equation on their own: all of them read the handle's error flag now, so they need a valid communicator."""
+    monkeypatch.setenv("FEAB_CLUSTER", "0")
+    xyz, tri = meshes.icosphere(24)
+    ob = meshes.boundary_flags(len(xyz), tri)
+    F = feab.Feab(real=real)
+    F.set_mesh(xyz, tri, ob)
+    for eq in (0, 1, 2, 3):
+        F.set_equation(eq)
+        F.clear()
+        F.set_values(seeded(len(xyz)))
+        F.step(1)
+        for kernel in range(4):
+            ms, nbytes = F.time_kernel(kernel, 3)
+            assert ms > 0 and nbytes > 0, (eq, kernel)
+        F.step(1)
+    assert np.isfinite(F.get_values()).all()
+    F.close()
