@@ -8,7 +8,7 @@ dominant PCG kernel, next to the reference's Eigen CPU path.
 
 A "step" is one Gray-Scott time step (two Jacobi-PCG solves run to Eigen's stopping rule) of the whole mesh.
 `value` keeps the field device-resident (feab_step(NULL, K, 0)); `e2e` drives THE SAME K steps (state restored from a
-snapshot taken after the warm-up) through the reference-facing call with a pinned HOST values buffer, one host->device
+snapshot taken after the warm-up) through the reference-facing call with a HOST values buffer (a pageable array page-locked once via feab_register_host_values), one host->device
 and one device->host copy per step.  Before anything is timed the same handle type / loop driver / world size runs the
 SURVEY 8(d) protocol on small meshes against the fp64 CPU oracle (`parity`, bar 1e-8 relative L2 per step); a parity
 failure makes the run exit non-zero.  Prints ONE JSON line on rank 0.
@@ -442,7 +442,10 @@ def main():
     seed_protocol(F, V, warm)
     # snapshot: both timed legs advance the SAME steps (warm .. warm + K - 1) from the same state
     snap_u, snap_v, snap_vals = F.get_state(0), F.get_state(1), F.get_values()
-    host = torch.empty(V, dtype=torch.float32).pin_memory()
+    # surface->values on the host: an ordinary (pageable) array, like the reference's std::vector<float>; the documented binding
+    # page-locks it once per surface load through the C ABI (feab_register_host_values -> cudaHostRegister), further down
+    host_np = np.zeros(V, dtype=np.float32)
+    host = torch.from_numpy(host_np)
     if world > 1:
         # surface->values complete on rank 0's host: every owner contributes its nodes
         row_node, _ = F.mg_maps()
@@ -478,6 +481,22 @@ def main():
         sys.stderr.write(f"[rank {rank}] pcg phase profile: {json.dumps(prof)}\n")
     else:
         prof = None
+    # --- the same call from the UNREGISTERED pageable array, once, for the record (one GPU; 2 steps, not part of any timed leg) ---
+    sync_mode = feab.SYNC_ROOT if world > 1 else feab.SYNC_FULL
+    pageable_sps = None
+    if world == 1:
+        keep = host_np.copy()
+        F.set_state(0, snap_u)
+        F.set_state(1, snap_v)
+        F.set_values(snap_vals)
+        F.step_ptr(host_np.ctypes.data, 1, sync_mode)
+        t0 = time.perf_counter()
+        for _ in range(2):
+            F.step_ptr(host_np.ctypes.data, 1, sync_mode)
+        torch.cuda.synchronize()
+        pageable_sps = 2.0 / (time.perf_counter() - t0)
+        host_np[:] = keep
+    F.register_host_values(host_np)
     # --- end-to-end through the reference-facing call with HOST buffers: the same K steps again ---
     F.set_state(0, snap_u)
     F.set_state(1, snap_v)
@@ -487,10 +506,11 @@ def main():
     for _ in range(args.steps):
         # one GPU: H2D of values, one step, D2H of values, synchronised.  Partitioned: surface->values lives on rank 0's host
         # (FEAB_SYNC_ROOT): rank 0 uploads, NVLink forwards to the peers, only rank 0 downloads the result
-        F.step_ptr(host.data_ptr(), 1, feab.SYNC_ROOT if world > 1 else feab.SYNC_FULL)
+        F.step_ptr(host_np.ctypes.data, 1, sync_mode)
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
     barrier()
+    F.register_host_values(None)             # the array is about to go out of use: undo the page-lock first
     its_e2e = F.stats()["iterations"]
     if step_ms is not None:
         step_ms["e2e_leg_last_step"] = F.pcg_profile(reset=False)["step_ms"]
@@ -589,6 +609,8 @@ def main():
                 "us_per_pcg_iteration": (solve_ms * 1e3 / max(1, its[0] + its[1])) if solve_ms else None,
                 "e2e": {"value": e2e_value, "unit": "steps/s", "h2d_bytes_per_step": 4 * V, "d2h_bytes_per_step": 4 * V,
                         "mode": "host buffers on rank 0 (FEAB_SYNC_ROOT), peers fed over NVLink" if world > 1 else "host buffers, full sync",
+                        "host_memory": "pageable numpy array, page-locked once through the C ABI (feab_register_host_values -> cudaHostRegister), as the documented binding does with surface->values",
+                        "pageable_unregistered_value": pageable_sps,
                         "pcg_iterations_last_step": its_e2e, "same_steps_as_value": list(its_e2e) == list(its), "le_value": e2e_value <= value},
                 "gpu_launches": launches_all, "pcg_phase_profile": prof, "step_phase_ms": step_ms, "parity": parity, "roofline": roof, "cpu_baseline": cpu, "clocks": clocks}
         emit(line)

@@ -2179,6 +2179,19 @@ struct FeabHandle {
     std::string err;
     std::unique_ptr<feab::SolverBase> impl;
     cudaDeviceProp prop;
+    void* reg_ptr = nullptr;   // host range page-locked by feab_register_host_values (undone on re-registration / destroy)
+    void unregister_host() {
+        if (reg_ptr) {
+            cudaSetDevice(device);
+            cudaHostUnregister(reg_ptr);
+            cudaGetLastError();
+            reg_ptr = nullptr;
+        }
+    }
+    ~FeabHandle() {
+        impl.reset();          // the solver drains its stream first: no copy may still read the range
+        unregister_host();
+    }
 };
 
 static thread_local std::string g_create_err;
@@ -2277,6 +2290,19 @@ int feab_values_device(FeabHandle* h, const float** out) {
     if (!out) return FEAB_EINVAL;
     FEAB_TRY(h, *out = h->impl->values_device());
 }
+static void register_host_values(FeabHandle* h, float* values, int64_t count) {
+    h->unregister_host();
+    if (!values) return;
+    if (count <= 0) throw feab::Err{FEAB_EINVAL, "register_host_values: count <= 0"};
+    cudaError_t e = cudaSetDevice(h->device);
+    if (e == cudaSuccess) e = cudaHostRegister(values, (size_t)count * sizeof(float), cudaHostRegisterPortable);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        throw feab::Err{(int)e, std::string("register_host_values: cudaHostRegister: ") + cudaGetErrorString(e)};
+    }
+    h->reg_ptr = values;
+}
+int feab_register_host_values(FeabHandle* h, float* values, int64_t count) { FEAB_TRY(h, register_host_values(h, values, count)); }
 int feab_brush(FeabHandle* h, const int64_t* nodes, int64_t count, float strength) { FEAB_TRY(h, h->impl->brush(nodes, count, strength)); }
 int feab_step(FeabHandle* h, float* values, int nsteps, int sync) { FEAB_TRY(h, h->impl->step(values, nsteps, sync)); }
 int feab_unstable(FeabHandle* h, int* out) {

@@ -23,6 +23,7 @@ SYNC_NONE, SYNC_FULL, SYNC_ROOT = 0, 1, 2
 
 # every symbol include/feab.h declares (checked by tests/test_abi.py without a GPU)
 ABI_SYMBOLS = [
+    "feab_register_host_values",
     "feab_create", "feab_destroy", "feab_last_error", "feab_set_mesh", "feab_set_mesh_ex", "feab_set_boundary_condition", "feab_assemble",
     "feab_get_counts", "feab_get_idx_map", "feab_get_csr", "feab_set_equation", "feab_set_params", "feab_get_params",
     "feab_set_solver_options", "feab_get_solver_options", "feab_clear", "feab_set_values", "feab_get_values", "feab_brush",
@@ -212,6 +213,15 @@ class Feab:
         else:
             assert values.dtype == np.float32 and values.flags.c_contiguous and values.shape[0] == self.V
             self._ck(self.lib.feab_step(self.h, C.c_void_p(values.ctypes.data), C.c_int(nsteps), C.c_int(int(sync_values))))   # FEAB_SYNC_*
+
+    def register_host_values(self, values):
+        """feab_register_host_values: page-locks the (pageable) float32 array the caller will pass to step(values=...) --
+        what the C++ binding does with surface->values after a surface load.  None undoes it.  Keep `values` alive."""
+        if values is None:
+            self._ck(self.lib.feab_register_host_values(self.h, None, C.c_int64(0)))
+            return
+        assert values.dtype == np.float32 and values.flags.c_contiguous
+        self._ck(self.lib.feab_register_host_values(self.h, C.c_void_p(values.ctypes.data), C.c_int64(values.size)))
 
     def step_ptr(self, host_ptr: int, nsteps: int, sync_values: bool):
         """Same with a raw host pointer (e.g. pinned torch memory)."""

@@ -105,6 +105,8 @@ class CUDASolver : public Solver {
 
    private:
     FeabHandle* h_ = nullptr;
+    const float* reg_values_ = nullptr;   // what feab_register_host_values last page-locked
+    size_t reg_count_ = 0;
     std::vector<unsigned long long> mesh_sig_, asm_sig_;
 
     void check(int rc, const char* what) {
@@ -127,6 +129,13 @@ class CUDASolver : public Solver {
     void sync_context() {
         FEMContext& c = *fem_ctx;
         Surface& s = *c.surface;
+        // surface->values is the array every feab_step copies from and to: page-lock it whenever the vector moved or changed
+        // size (a surface load); an empty vector undoes the registration
+        if (s.values.data() != reg_values_ || s.values.size() != reg_count_) {
+            check(feab_register_host_values(h_, s.values.empty() ? nullptr : s.values.data(), (int64_t)s.values.size()), "feab_register_host_values");
+            reg_values_ = s.values.data();
+            reg_count_ = s.values.size();
+        }
         static_assert(sizeof(s.vertices[0]) == 3 * sizeof(float), "Surface::vertices must hold 3 packed floats");
         static_assert(sizeof(s.triangles[0]) == 3 * sizeof(unsigned int), "Triangle must hold 3 packed indices");
         std::vector<unsigned long long> msig = {(unsigned long long)(uintptr_t)&s, s.vertices.size(), s.triangles.size(),

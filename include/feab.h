@@ -139,6 +139,13 @@ int feab_clear(FeabHandle* h);
 /* surface->values (include/Utils/Surface.hpp:38), device-resident here */
 int feab_set_values(FeabHandle* h, const float* values_num_nodes);
 int feab_get_values(FeabHandle* h, float* values_num_nodes);
+/* Page-locks the host array behind surface->values (std::vector<float>, include/Utils/Surface.hpp:38) so that feab_step's
+ * copies of values_inout run at full PCIe speed and asynchronously: cudaHostRegister(values, count * 4, Portable).  The
+ * binding calls it whenever surface->values.data() or its size changes -- that only happens on a surface load
+ * (src/Application.cpp:593-596, :620-623) -- and feab_step is then given that same pointer.  values == NULL or a new
+ * registration undoes the previous one; feab_destroy undoes the last.  Without it feab_step still works from pageable
+ * memory (staged by the driver, slower).  The caller keeps the array alive and unmoved while it is registered. */
+int feab_register_host_values(FeabHandle* h, float* values, int64_t count);
 /* GPUSolver::brush(idx, strength) (include/FEM/GPUSolver.hpp:41, src/FEM/GPUSolver.cpp:44-51) /
  * Application::brush's write surface->values[node] = strength (src/Application.cpp:722) for many nodes */
 int feab_brush(FeabHandle* h, const int64_t* nodes, int64_t count, float strength);

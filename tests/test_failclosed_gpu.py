@@ -103,3 +103,34 @@ def test_measurement_hook_runs_every_kernel(real, monkeypatch):
         F.step(1)
     assert np.isfinite(F.get_values()).all()
     F.close()
+
+
+def test_registered_host_values_give_the_same_steps_as_pageable_ones():
+    """feab_register_host_values page-locks the caller's surface->values array (cudaHostRegister); the numbers must not
+    depend on it, re-registration and un-registration must be clean, and a handle can be destroyed while registered."""
+    xyz, tri = meshes.icosphere(24)
+    ob = meshes.boundary_flags(len(xyz), tri)
+    V = len(xyz)
+    outs = []
+    for registered in (False, True, True):
+        F = feab.Feab(real=64)
+        F.set_mesh(xyz, tri, ob)
+        F.set_equation(3)
+        F.clear()
+        host = seeded(V).copy()
+        other = np.zeros(V, np.float32)
+        if registered:
+            F.register_host_values(other)
+            F.register_host_values(host)          # replaces the first registration
+        for _ in range(4):
+            F.step(1, values=host, sync_values=True)
+        outs.append(host.copy())
+        if registered and len(outs) == 2:
+            F.register_host_values(None)          # explicit un-registration; the third round leaves it to feab_destroy
+            F.step(1, values=host, sync_values=True)
+        with pytest.raises(feab.FeabError):
+            F.lib.feab_register_host_values.argtypes = None
+            F._ck(F.lib.feab_register_host_values(F.h, host.ctypes.data_as(__import__("ctypes").c_void_p), __import__("ctypes").c_int64(0)))
+        F.close()
+    assert np.array_equal(outs[0], outs[1]) and np.array_equal(outs[0], outs[2])
+    assert np.isfinite(outs[0]).all() and outs[0].any()
